@@ -1,0 +1,65 @@
+"""ctypes binding of libevent3dgs.so (the C ABI declared in include/event3dgs.h).
+
+There is no fallback: if the CUDA library is missing or fails to load, importing a symbol from
+here raises -- the product path never runs on the CPU or through the oracle.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libevent3dgs.so")
+
+ALLOC_FN = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+
+_vp, _i, _f, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t
+
+# name -> (restype, argtypes); kept in one table so tests can check it against the header
+SIGNATURES = {
+    "e3_error_string": (ctypes.c_char_p, [_i]),
+    "e3_version": (_i, []),
+    "e3_geometry_bytes": (_sz, [_i]),
+    "e3_image_bytes": (_sz, [_i, _i]),
+    "e3_binning_bytes": (_sz, [_i]),
+    "e3_rasterize_forward": (_i, [ALLOC_FN, _vp, ALLOC_FN, _vp, ALLOC_FN, _vp,
+                                  _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp,
+                                  _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _i, _vp, ctypes.POINTER(_i)]),
+    "e3_rasterize_backward": (_i, [_i, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp,
+                                   _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                   _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
+    "e3_geometry_ptr": (_vp, [_vp, _i, _i]),
+    "e3_binning_ptr": (_vp, [_vp, _i, _i]),
+    "e3_image_ptr": (_vp, [_vp, _i, _i, _i]),
+}
+
+_lib = None
+
+
+def build(verbose=False):
+    """Compile every .cu under csrc/ for sm_100a into libevent3dgs.so (in-tree)."""
+    cmd = ["make", "-f", os.path.join(_HERE, "csrc", "Makefile")]
+    subprocess.check_call(cmd, stdout=None if verbose else subprocess.DEVNULL)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "event_3dgs_b200: %s is missing. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). There is no CPU fallback." % LIB_PATH)
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)     # AttributeError if the library does not export it
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(code):
+    if code != 0:
+        msg = lib().e3_error_string(code)
+        raise RuntimeError(msg.decode() if msg else "event3dgs error %d" % code)

@@ -1,0 +1,235 @@
+// extern "C" entry points of libevent3dgs.so (declared in include/event3dgs.h).
+// Host orchestration mirrors CudaRasterizer::Rasterizer::forward / backward
+// (cuda_rasterizer/rasterizer_impl.cu:198-336, 340-434).
+#include "common.cuh"
+#include "../../include/event3dgs.h"
+
+#include <cstdio>
+
+namespace {
+
+// rasterizer_impl.cu:35-50: number of tile-id bits the sort has to cover
+uint32_t higher_msb(uint32_t n)
+{
+	uint32_t msb = sizeof(n) * 4, step = msb;
+	while (step > 1) {
+		step /= 2;
+		if (n >> msb) msb += step; else msb -= step;
+	}
+	if (n >> msb) msb++;
+	return msb;
+}
+
+E3Frame make_frame(int P, int D, int M, int C, int W, int H, float tan_fovx, float tan_fovy, float mod)
+{
+	E3Frame f;
+	f.P = P; f.D = D; f.M = M; f.C = C; f.W = W; f.H = H;
+	f.gx = (W + E3_TILE_X - 1) / E3_TILE_X;
+	f.gy = (H + E3_TILE_Y - 1) / E3_TILE_Y;
+	f.tan_fovx = tan_fovx; f.tan_fovy = tan_fovy;
+	f.focal_y = H / (2.0f * tan_fovy);     // rasterizer_impl.cu:222-223
+	f.focal_x = W / (2.0f * tan_fovx);
+	f.scale_modifier = mod;
+	return f;
+}
+
+#define E3_CHECK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (int)e__; } while (0)
+// debug mode: sync-and-check after every stage, like CHECK_CUDA (auxiliary.h:166-173)
+#define E3_STAGE(expr) do { E3_CHECK(expr); if (debug) { E3_CHECK(cudaStreamSynchronize(st)); } } while (0)
+
+}  // namespace
+
+extern "C" {
+
+int e3_version(void) { return 100; }
+
+const char* e3_error_string(int code)
+{
+	switch (code) {
+	case 0: return "success";
+	case E3_ERR_BAD_ARGUMENT: return "event3dgs: bad argument";
+	case E3_ERR_ALLOC_FAILED: return "event3dgs: workspace allocation callback returned NULL";
+	case E3_ERR_PREFILTERED: return "Point is filtered although prefiltered is set. This shouldn't happen!";
+	case E3_ERR_UNSUPPORTED: return "For non-RGB, provide precomputed Gaussian colors!";
+	}
+	if (code > 0) return cudaGetErrorString((cudaError_t)code);
+	return "event3dgs: unknown error";
+}
+
+size_t e3_geometry_bytes(int P)
+{
+	char* end = nullptr;
+	E3GeomState::carve(nullptr, (size_t)P, &end);
+	return (size_t)end + 256;
+}
+
+size_t e3_image_bytes(int width, int height)
+{
+	char* end = nullptr;
+	const size_t T = (size_t)((width + E3_TILE_X - 1) / E3_TILE_X) * ((height + E3_TILE_Y - 1) / E3_TILE_Y);
+	E3ImageState::carve(nullptr, (size_t)width * height, T, &end);
+	return (size_t)end + 256;
+}
+
+size_t e3_binning_bytes(int num_rendered)
+{
+	char* end = nullptr;
+	E3BinState::carve(nullptr, (size_t)num_rendered, &end);
+	return (size_t)end + 256;
+}
+
+int e3_rasterize_forward(
+	e3_alloc_fn geometry_alloc, void* geometry_ctx,
+	e3_alloc_fn binning_alloc, void* binning_ctx,
+	e3_alloc_fn image_alloc, void* image_ctx,
+	int P, int D, int M, int channels,
+	const float* background, int width, int height,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy, int prefiltered,
+	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	if (num_rendered_host) *num_rendered_host = 0;
+	if (P < 0 || width <= 0 || height <= 0 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
+	if (P == 0) return 0;
+	if (!geometry_alloc || !binning_alloc || !image_alloc || !means3D || !opacities || !background ||
+		!viewmatrix || !projmatrix || !out_color || !radii || !num_rendered_host)
+		return E3_ERR_BAD_ARGUMENT;
+	if (!colors_precomp && (!shs || !cam_pos)) return E3_ERR_BAD_ARGUMENT;
+	if (!colors_precomp && channels != 3) return E3_ERR_UNSUPPORTED;
+	if (!cov3D_precomp && (!scales || !rotations)) return E3_ERR_BAD_ARGUMENT;
+
+	E3Frame f = make_frame(P, D, M, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
+	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
+
+	char* gbuf = geometry_alloc(geometry_ctx, e3_geometry_bytes(P));
+	if (!gbuf) return E3_ERR_ALLOC_FAILED;
+	E3GeomState g = E3GeomState::carve(gbuf, P);
+	char* ibuf = image_alloc(image_ctx, e3_image_bytes(width, height));
+	if (!ibuf) return E3_ERR_ALLOC_FAILED;
+	E3ImageState im = E3ImageState::carve(ibuf, N, T);
+
+	E3_CHECK(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), st));
+	E3_STAGE(e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+		viewmatrix, projmatrix, cam_pos, prefiltered != 0, radii, g, st));
+
+	// depth order of the Gaussians (culled ones carry key 0xffffffff and emit nothing)
+	int dres = 0;
+	E3_STAGE(e3_radix_sort_pairs(g.dkey, g.dval, (size_t)P, 32, g.sort_counts, g.scan_tmp, &dres, st));
+	const uint32_t* order = g.dval[dres];
+	// instance offsets in depth order; grand total = num_rendered
+	E3_STAGE(e3_exclusive_scan_u32(g.tiles_touched, order, g.offsets, (size_t)P, g.scan_tmp,
+		reinterpret_cast<uint32_t*>(g.flags), st));
+
+	int h_flags[2] = { 0, 0 };
+	E3_CHECK(cudaMemcpyAsync(h_flags, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+	E3_CHECK(cudaStreamSynchronize(st));        // the reference's blocking read of R (rasterizer_impl.cu:281)
+	if (h_flags[1]) return E3_ERR_PREFILTERED;
+	const int R = h_flags[0];
+	*num_rendered_host = R;
+
+	char* bbuf = binning_alloc(binning_ctx, e3_binning_bytes(R));
+	if (!bbuf) return E3_ERR_ALLOC_FAILED;
+	E3BinState b = E3BinState::carve(bbuf, (size_t)R);
+
+	E3_STAGE(e3_launch_emit_instances(P, order, g.offsets, g.tiles_touched, g.rect, f.gx, b.tkey[0], b.val[0], st));
+	int bres = 0;
+	E3_STAGE(e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, (int)higher_msb((uint32_t)T), b.sort_counts, b.scan_tmp, &bres, st));
+	if (bres != 0) {
+		// keep the sorted lists in slot 0 so that backward finds them without extra state
+		E3_CHECK(cudaMemcpyAsync(b.tkey[0], b.tkey[1], (size_t)R * 4, cudaMemcpyDeviceToDevice, st));
+		E3_CHECK(cudaMemcpyAsync(b.val[0], b.val[1], (size_t)R * 4, cudaMemcpyDeviceToDevice, st));
+	}
+	E3_STAGE(e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
+	E3_STAGE(e3_launch_render_forward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
+	return 0;
+}
+
+int e3_rasterize_backward(
+	int P, int D, int M, int R, int channels,
+	const float* background, int width, int height,
+	const float* means3D, const float* shs, const float* colors_precomp,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+	int debug, void* stream)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	if (P < 0 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
+	if (P == 0) return 0;
+	if (!geometry_buffer || !image_buffer || (R > 0 && !binning_buffer) || !radii || !means3D || !dL_dpix ||
+		!dL_dmean2D || !dL_dopacity || !dL_dcolor || !dL_dmean3D || !dL_dcov3D || !viewmatrix || !projmatrix)
+		return E3_ERR_BAD_ARGUMENT;
+	if (shs && (!dL_dsh || !campos)) return E3_ERR_BAD_ARGUMENT;
+	if (scales && (!rotations || !dL_dscale || !dL_drot)) return E3_ERR_BAD_ARGUMENT;
+	(void)colors_precomp;   // colours live in the packed records written by the forward
+
+	E3Frame f = make_frame(P, D, M, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
+	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
+	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
+	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
+	if (R > 0) {
+		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
+		E3_STAGE(e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+			dL_dpix, g.acc, st));
+	}
+	E3_STAGE(e3_launch_preprocess_backward(f, means3D, radii, shs, scales, rotations, cov3D_precomp, viewmatrix,
+		projmatrix, campos, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh,
+		dL_dscale, dL_drot, st));
+	return 0;
+}
+
+int e3_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+	uint8_t* present, void* stream)
+{
+	(void)projmatrix;   // the reference's test only uses the view-space depth (auxiliary.h:154)
+	if (P < 0) return E3_ERR_BAD_ARGUMENT;
+	if (P == 0) return 0;
+	if (!means3D || !viewmatrix || !present) return E3_ERR_BAD_ARGUMENT;
+	E3_CHECK(e3_launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream));
+	return 0;
+}
+
+void* e3_geometry_ptr(char* geometry_buffer, int P, int which)
+{
+	E3GeomState g = E3GeomState::carve(geometry_buffer, (size_t)P);
+	switch (which) {
+	case 0: return g.depths;
+	case 1: return g.rec;
+	case 2: return g.cov3D;
+	case 3: return g.tiles_touched;
+	case 4: return g.dval[0];   // 4 passes of the depth sort end in slot 0
+	case 5: return g.rgb;
+	case 6: return g.clamped;
+	}
+	return nullptr;
+}
+
+void* e3_binning_ptr(char* binning_buffer, int num_rendered, int which)
+{
+	E3BinState b = E3BinState::carve(binning_buffer, (size_t)num_rendered);
+	switch (which) {
+	case 0: return b.val[0];
+	case 1: return b.tkey[0];
+	}
+	return nullptr;
+}
+
+void* e3_image_ptr(char* image_buffer, int width, int height, int which)
+{
+	const size_t T = (size_t)((width + E3_TILE_X - 1) / E3_TILE_X) * ((height + E3_TILE_Y - 1) / E3_TILE_Y);
+	E3ImageState im = E3ImageState::carve(image_buffer, (size_t)width * height, T);
+	switch (which) {
+	case 0: return im.final_T;
+	case 1: return im.n_contrib;
+	case 2: return im.ranges;
+	}
+	return nullptr;
+}
+
+}  // extern "C"

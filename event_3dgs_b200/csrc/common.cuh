@@ -1,0 +1,152 @@
+// Shared device helpers and private state layouts of libevent3dgs (sm_100a).
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cuda_runtime.h>
+
+#define E3_TILE_X 16
+#define E3_TILE_Y 16
+#define E3_TILE_PIX 256
+#define E3_FULL 0xffffffffu
+
+// Per-Gaussian gradient accumulator written by the backward blend and consumed by the
+// backward preprocess: 12 floats (48 B, 16-byte aligned) so that one warp's reduced values
+// land in one or two 32-byte sectors.
+//   0,1 dL/dmean2D (x,y)   2,3,4 dL/dconic (xx,xy,yy)   5 dL/dopacity   6.. dL/dcolour
+#define E3_ACC_STRIDE 12
+
+static inline size_t e3_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+template <typename T>
+static inline void e3_carve(char*& p, T*& out, size_t count)
+{
+	p = reinterpret_cast<char*>(e3_align_up(reinterpret_cast<size_t>(p), 256));
+	out = reinterpret_cast<T*>(p);
+	p += count * sizeof(T);
+}
+
+// Radix-sort scratch: `counts` holds one digit histogram per sort block.
+#define E3_SORT_THREADS 256
+#define E3_SORT_ITEMS 16
+#define E3_SORT_TILE (E3_SORT_THREADS * E3_SORT_ITEMS)
+#define E3_SCAN_THREADS 256
+#define E3_SCAN_ITEMS 8
+#define E3_SCAN_TILE (E3_SCAN_THREADS * E3_SCAN_ITEMS)
+
+static inline size_t e3_sort_blocks(size_t n) { return (n + E3_SORT_TILE - 1) / E3_SORT_TILE; }
+static inline size_t e3_scan_blocks(size_t n) { return (n + E3_SCAN_TILE - 1) / E3_SCAN_TILE; }
+
+struct E3GeomState {
+	float* depths;            // [P] view-space z
+	float4* rec;              // [3P] packed per-Gaussian record
+	float* cov3D;             // [6P]
+	float* rgb;               // [3P] SH colours (only when shs given)
+	uint8_t* clamped;         // [3P]
+	uint32_t* tiles_touched;  // [P]
+	uint2* rect;              // [P] (xmin | xmax<<16, ymin | ymax<<16)
+	uint32_t* dkey[2];        // [P] depth keys, ping-pong
+	uint32_t* dval[2];        // [P] Gaussian ids in depth order, ping-pong
+	uint32_t* offsets;        // [P] exclusive instance offsets in depth order
+	uint32_t* sort_counts;    // [256 * sort_blocks(P)]
+	uint32_t* scan_tmp;       // [max(scan_blocks(256*sort_blocks(P)), scan_blocks(P)) + 2]
+	float* acc;               // [P * E3_ACC_STRIDE] backward accumulators
+	int* flags;               // [4]: 0 num_rendered, 1 prefiltered-violation
+	static E3GeomState carve(char* p, size_t P, char** end = nullptr)
+	{
+		E3GeomState s;
+		e3_carve(p, s.depths, P);
+		e3_carve(p, s.rec, 3 * P);
+		e3_carve(p, s.cov3D, 6 * P);
+		e3_carve(p, s.rgb, 3 * P);
+		e3_carve(p, s.clamped, 3 * P);
+		e3_carve(p, s.tiles_touched, P);
+		e3_carve(p, s.rect, P);
+		e3_carve(p, s.dkey[0], P);
+		e3_carve(p, s.dkey[1], P);
+		e3_carve(p, s.dval[0], P);
+		e3_carve(p, s.dval[1], P);
+		e3_carve(p, s.offsets, P);
+		size_t nc = 256 * e3_sort_blocks(P);
+		e3_carve(p, s.sort_counts, nc);
+		size_t nt = e3_scan_blocks(nc) > e3_scan_blocks(P) ? e3_scan_blocks(nc) : e3_scan_blocks(P);
+		e3_carve(p, s.scan_tmp, nt + 2);
+		e3_carve(p, s.acc, P * E3_ACC_STRIDE);
+		e3_carve(p, s.flags, 4);
+		if (end) *end = p;
+		return s;
+	}
+};
+
+struct E3ImageState {
+	float* final_T;       // [N]
+	uint32_t* n_contrib;  // [N]
+	uint2* ranges;        // [T]
+	static E3ImageState carve(char* p, size_t N, size_t T, char** end = nullptr)
+	{
+		E3ImageState s;
+		e3_carve(p, s.final_T, N);
+		e3_carve(p, s.n_contrib, N);
+		e3_carve(p, s.ranges, T);
+		if (end) *end = p;
+		return s;
+	}
+};
+
+struct E3BinState {
+	uint32_t* tkey[2];      // [R] tile ids, ping-pong
+	uint32_t* val[2];       // [R] Gaussian ids, ping-pong
+	uint32_t* sort_counts;  // [256 * sort_blocks(R)]
+	uint32_t* scan_tmp;     // [scan_blocks(256*sort_blocks(R)) + 2]
+	static E3BinState carve(char* p, size_t R, char** end = nullptr)
+	{
+		E3BinState s;
+		e3_carve(p, s.tkey[0], R);
+		e3_carve(p, s.tkey[1], R);
+		e3_carve(p, s.val[0], R);
+		e3_carve(p, s.val[1], R);
+		size_t nc = 256 * e3_sort_blocks(R);
+		e3_carve(p, s.sort_counts, nc);
+		e3_carve(p, s.scan_tmp, e3_scan_blocks(nc) + 2);
+		if (end) *end = p;
+		return s;
+	}
+};
+
+// ---- internal launchers (defined in the .cu files) ----
+struct E3Frame {
+	int P, D, M, C, W, H, gx, gy;
+	float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+};
+
+cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
+	const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
+	const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
+	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st);
+cudaError_t e3_launch_mark_visible(int P, const float* means3D, const float* viewmatrix,
+	uint8_t* present, cudaStream_t st);
+cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D,
+	const int* radii, const float* shs, const float* scales, const float* rotations,
+	const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+	const float* campos, const E3GeomState& g, float* dL_dmean2D, float* dL_dconic,
+	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+	float* dL_dscale, float* dL_drot, cudaStream_t st);
+
+// out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (optional, device) = sum of all
+cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint32_t* out,
+	size_t n, uint32_t* tmp, uint32_t* total, cudaStream_t st);
+// Stable LSD radix sort of (key,val) pairs over key bits [0,end_bit). Returns the index (0/1)
+// of the ping-pong buffer that holds the result in *result_buf.
+cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
+	uint32_t* counts, uint32_t* scan_tmp, int* result_buf, cudaStream_t st);
+cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_t* offsets,
+	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals,
+	cudaStream_t st);
+cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges, size_t T,
+	cudaStream_t st);
+
+cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges,
+	const uint32_t* point_list, const float4* rec, const float* bg, float* final_T,
+	uint32_t* n_contrib, float* out_color, cudaStream_t st);
+cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges,
+	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
+	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st);

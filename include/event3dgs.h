@@ -1,0 +1,147 @@
+/*
+ * event3dgs.h -- C ABI of libevent3dgs.so, the B200 (sm_100a) implementation of the
+ * Event-3DGS differentiable splatting hot path.
+ *
+ * Plain pointers and sizes only; no torch, pybind or C++ types. Every pointer is a DEVICE
+ * pointer unless its name ends in _host. All kernels are enqueued on `stream`
+ * (a cudaStream_t passed as void*; NULL = the legacy default stream the reference uses).
+ * The library allocates no device memory of its own: workspaces come from the caller through
+ * the e3_alloc_fn callbacks (forward) or are handed back as pointers (backward), exactly like
+ * the reference's resize-callback scheme. Return value: 0 on success, otherwise a cudaError_t
+ * value (> 0) or an E3_ERR_* code (< 0); e3_error_string() explains both.
+ *
+ * Reference citations are relative to /root/reference/submodules/diff-gaussian-rasterization/.
+ */
+#ifndef EVENT3DGS_H_INCLUDED
+#define EVENT3DGS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define E3_API __attribute__((visibility("default")))
+#else
+#define E3_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define E3_ERR_BAD_ARGUMENT  (-1)   /* shape / pointer contract violated */
+#define E3_ERR_ALLOC_FAILED  (-2)   /* an e3_alloc_fn returned NULL */
+#define E3_ERR_PREFILTERED   (-3)   /* a point was culled although `prefiltered` was set
+                                       (the reference __trap()s, cuda_rasterizer/auxiliary.h:156-160) */
+#define E3_ERR_UNSUPPORTED   (-4)   /* e.g. SH colours requested with channels != 3
+                                       (cuda_rasterizer/rasterizer_impl.cu:242-245) */
+
+E3_API const char* e3_error_string(int code);
+E3_API int e3_version(void);
+
+/* Replaces std::function<char*(size_t)> of CudaRasterizer::Rasterizer::forward
+ * (cuda_rasterizer/rasterizer.h:32-34) and resizeFunctional (rasterize_points.cu:27-33):
+ * must return a device buffer of at least `bytes` bytes, 256-byte aligned, that stays alive
+ * until the matching backward has run. */
+typedef char* (*e3_alloc_fn)(void* ctx, size_t bytes);
+
+/* Sizes of the three opaque state buffers (replace required<GeometryState>(P),
+ * required<ImageState>(N), required<BinningState>(R), cuda_rasterizer/rasterizer_impl.h:67-73).
+ * The layouts are private to this library and differ from the reference's. */
+E3_API size_t e3_geometry_bytes(int P);
+E3_API size_t e3_image_bytes(int width, int height);
+E3_API size_t e3_binning_bytes(int num_rendered);
+
+/* Replaces CudaRasterizer::Rasterizer::forward (cuda_rasterizer/rasterizer.h:31-54,
+ * rasterizer_impl.cu:198-336) as called by RasterizeGaussiansCUDA (rasterize_points.cu:35-115).
+ * Same arguments in the same order, plus: `channels` (3 = the reference's NUM_CHANNELS,
+ * config.h:15; 1 = single-channel "gray" colours, only with colors_precomp), the three
+ * callback contexts, `stream`. Unused optional inputs are NULL (the reference passes the data
+ * pointer of an empty tensor). out_color is [channels,H,W]; radii is int32[P] and must not be
+ * NULL. *num_rendered_host receives R (this call synchronises the stream once to read R, as the
+ * reference does at rasterizer_impl.cu:281). P == 0 is the caller's short-circuit
+ * (rasterize_points.cu:81): the function then only returns 0 with R = 0. */
+E3_API int e3_rasterize_forward(
+	e3_alloc_fn geometry_alloc, void* geometry_ctx,
+	e3_alloc_fn binning_alloc, void* binning_ctx,
+	e3_alloc_fn image_alloc, void* image_ctx,
+	int P, int D, int M, int channels,
+	const float* background,
+	int width, int height,
+	const float* means3D,
+	const float* shs,
+	const float* colors_precomp,
+	const float* opacities,
+	const float* scales,
+	float scale_modifier,
+	const float* rotations,
+	const float* cov3D_precomp,
+	const float* viewmatrix,
+	const float* projmatrix,
+	const float* cam_pos,
+	float tan_fovx, float tan_fovy,
+	int prefiltered,
+	float* out_color,
+	int* radii,
+	int debug,
+	void* stream,
+	int* num_rendered_host);
+
+/* Replaces CudaRasterizer::Rasterizer::backward (cuda_rasterizer/rasterizer.h:56-84,
+ * rasterizer_impl.cu:340-434) as called by RasterizeGaussiansBackwardCUDA
+ * (rasterize_points.cu:117-196). Differences from the reference, all in the caller's favour:
+ * the nine gradient arrays need NOT be zero-filled (every row is written, rows of culled
+ * Gaussians with zeros), and dL_dconic may be NULL (it is an internal quantity there).
+ * Shapes: dL_dpix [channels,H,W]; dL_dmean2D [P,3] (z = 0); dL_dopacity [P]; dL_dcolor
+ * [P,channels]; dL_dmean3D [P,3]; dL_dcov3D [P,6]; dL_dsh [P,M,3]; dL_dscale [P,3]; dL_drot [P,4]. */
+E3_API int e3_rasterize_backward(
+	int P, int D, int M, int R, int channels,
+	const float* background,
+	int width, int height,
+	const float* means3D,
+	const float* shs,
+	const float* colors_precomp,
+	const float* scales,
+	float scale_modifier,
+	const float* rotations,
+	const float* cov3D_precomp,
+	const float* viewmatrix,
+	const float* projmatrix,
+	const float* campos,
+	float tan_fovx, float tan_fovy,
+	const int* radii,
+	char* geometry_buffer,
+	char* binning_buffer,
+	char* image_buffer,
+	const float* dL_dpix,
+	float* dL_dmean2D,
+	float* dL_dconic,
+	float* dL_dopacity,
+	float* dL_dcolor,
+	float* dL_dmean3D,
+	float* dL_dcov3D,
+	float* dL_dsh,
+	float* dL_dscale,
+	float* dL_drot,
+	int debug,
+	void* stream);
+
+/* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
+ * rasterizer_impl.cu:54-66,141-153): present[i] = view-space z > 0.2. present is uint8[P]. */
+E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,
+	const float* projmatrix, uint8_t* present, void* stream);
+
+/* Test / inspection hooks: device pointers into the opaque buffers of a finished forward.
+ * `which` (geometry): 0 depths f32[P], 1 packed records float4[3P] ({x,y,conic.x,conic.y},
+ *   {conic.z,opacity,c0,c1},{c2,-,-,-}), 2 cov3D f32[6P], 3 tiles_touched u32[P],
+ *   4 depth_order u32[P], 5 rgb f32[3P], 6 clamped u8[3P].
+ * `which` (binning): 0 point_list u32[R] (sorted Gaussian ids = the reference's point_list),
+ *   1 sorted tile ids u32[R] (high words of the reference's point_list_keys).
+ * `which` (image): 0 final_T f32[N], 1 n_contrib u32[N], 2 ranges uint2[T]. */
+E3_API void* e3_geometry_ptr(char* geometry_buffer, int P, int which);
+E3_API void* e3_binning_ptr(char* binning_buffer, int num_rendered, int which);
+E3_API void* e3_image_ptr(char* image_buffer, int width, int height, int which);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -147,4 +147,13 @@ void* ref_state_ptr(void* h, int which)
 	return nullptr;
 }
 
+// Copy `nbytes` of state array `which` into a caller-owned device buffer.
+int ref_copy_state(void* h, int which, void* dst, size_t nbytes)
+{
+	void* src = ref_state_ptr(h, which);
+	if (!src) return -1;
+	cudaDeviceSynchronize();
+	return (int)cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
+}
+
 }

@@ -1,0 +1,48 @@
+"""Shared helpers of the test-suite (not collected)."""
+import numpy as np
+
+from event_3dgs_b200 import synthetic as syn
+
+
+def scene_inputs(P, W, H, seed=0, kind="trained", view=3, channels=3, bg=(0.0, 0.0, 0.0), mean_radius_px=4.0):
+    """numpy inputs of one rasterizer call with precomputed colours."""
+    g = syn.make_gaussians(P, W, seed=seed, kind=kind, mean_radius_px=mean_radius_px)
+    a = syn.activate(g)
+    cam = syn.make_camera(view, 96, W, H)
+    rng = np.random.default_rng(seed + 7)
+    colors = rng.uniform(0, 1, (P, channels)).astype(np.float32)
+    return dict(means3D=a["means3D"], opacities=a["opacities"], scales=a["scales"], rotations=a["rotations"],
+                shs=a["shs"], colors=colors, viewmatrix=cam["world_view_transform"],
+                projmatrix=cam["full_proj_transform"], campos=cam["camera_center"],
+                bg=np.asarray(bg, np.float32), W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"])
+
+
+def smooth_dL(C, H, W, seed=0):
+    rng = np.random.default_rng(seed + 99)
+    yy, xx = np.mgrid[0:H, 0:W] / float(max(H, W))
+    ph = rng.uniform(0, 6.28, (C, 3))
+    out = np.stack([np.sin(5 * xx + ph[c, 0]) * np.cos(4 * yy + ph[c, 1]) + 0.3 * np.sin(9 * (xx + yy) + ph[c, 2])
+                    for c in range(C)])
+    return out.astype(np.float32)
+
+
+def oracle_forward(inp, use_sh=False, sh_degree=0, cov3D_precomp=None):
+    from oracle import raster_oracle as ro
+    kw = dict(scales=inp["scales"], rotations=inp["rotations"])
+    if cov3D_precomp is not None:
+        kw = dict(cov3D_precomp=cov3D_precomp)
+    if use_sh:
+        kw.update(shs=inp["shs"], sh_degree=sh_degree)
+    else:
+        kw.update(colors_precomp=inp["colors"])
+    return ro.rasterize_forward(inp["means3D"], inp["opacities"], inp["viewmatrix"], inp["projmatrix"], inp["campos"],
+                                inp["bg"], inp["W"], inp["H"], inp["tanfovx"], inp["tanfovy"], **kw)
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| -- the 'rel' of BASELINE.json's tolerances (relative to the array scale)."""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    d = np.abs(a - b).max() if a.size else 0.0
+    s = np.abs(b).max() if b.size else 0.0
+    return d / s if s > 0 else d

@@ -1,0 +1,263 @@
+"""-m gpu parity tests: the CUDA path (through the C ABI) against the reference's own CUDA build
+(oracle/_ref: bit-exact radii / sorted keys / point list / tile ranges / n_contrib / image) and
+against the CPU oracle (stated fp32 tolerances).
+
+Tolerances (BASELINE.json north_star): image 1e-5, gradients 1e-4, both relative to the array's
+max magnitude (rel_err in tests/common.py)."""
+import numpy as np
+import pytest
+import torch
+
+from tests.common import oracle_forward, rel_err, scene_inputs, smooth_dL
+
+pytestmark = pytest.mark.gpu
+
+IMG_TOL = 1e-5
+GRAD_TOL = 1e-4
+
+CASES = [
+    # P, W, H, seed, kind, bg
+    (10_000, 64, 64, 0, "trained", (0.0, 0.0, 0.0)),          # BASELINE config c1
+    (2_000, 100, 37, 1, "trained", (0.2, 0.5, 0.9)),          # ragged image size, non-black background
+    (50_000, 346, 260, 2, "trained", (0.0, 0.0, 0.0)),        # c2 shape, reduced P
+    (20_000, 346, 260, 3, "init", (1.0, 1.0, 1.0)),           # init-like: low opacity, no early stop
+]
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+@pytest.fixture(scope="module")
+def gc(cuda_dev):
+    from tests import gpu_common
+    return gpu_common
+
+
+@pytest.mark.parametrize("P,W,H,seed,kind,bg", CASES)
+def test_forward_bit_exact_vs_reference_cuda(gc, P, W, H, seed, kind, bg):
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/libref_dgr.so not built")
+    inp = scene_inputs(P, W, H, seed=seed, kind=kind, bg=bg)
+    fw = gc.ours_forward(inp)
+    st = gc.ours_state(fw, inp)
+    ref, R, out, radii = gc.ref_forward(inp)
+    assert fw["R"] == R
+    assert torch.equal(fw["radii"], radii)
+    assert torch.equal(st["tiles_touched"], ref.state("tiles_touched"))
+    vis = radii > 0
+    assert torch.equal(st["depths"].view(torch.int32)[vis], ref.state("depths").view(torch.int32)[vis])
+    assert torch.equal(st["cov3D"].view(torch.int32)[vis], ref.state("cov3D").view(P, 6).view(torch.int32)[vis])
+    rec = st["rec"]
+    assert torch.equal(rec[:, 0:2].contiguous().view(torch.int32)[vis], ref.state("means2D").view(P, 2).view(torch.int32)[vis])
+    co = ref.state("conic_opacity").view(P, 4)
+    assert torch.equal(rec[:, 2:6].contiguous().view(torch.int32)[vis], co.view(torch.int32)[vis])
+    # sorted (tile | depth) keys, values and ranges
+    assert torch.equal(st["point_list"], ref.state("point_list"))
+    assert torch.equal(gc.sorted_keys(st, radii), ref.state("point_list_keys"))
+    assert torch.equal(st["ranges"].reshape(-1), ref.state("ranges"))
+    # blend
+    assert torch.equal(st["n_contrib"], ref.state("n_contrib"))
+    assert torch.equal(st["final_T"].view(torch.int32), ref.state("accum_alpha").view(torch.int32))
+    assert torch.equal(fw["color"].view(torch.int32), out.view(torch.int32))
+
+
+@pytest.mark.parametrize("P,W,H,seed,kind,bg", CASES[:3])
+def test_forward_vs_cpu_oracle(gc, P, W, H, seed, kind, bg):
+    inp = scene_inputs(P, W, H, seed=seed, kind=kind, bg=bg)
+    fw = gc.ours_forward(inp)
+    st = gc.ours_state(fw, inp)
+    o = oracle_forward(inp)
+    assert fw["R"] == o["num_rendered"]
+    assert (_np(fw["radii"]) == o["radii"]).all()
+    assert (_np(st["point_list"]).view(np.uint32) == o["point_list"]).all()
+    assert (_np(gc.sorted_keys(st, fw["radii"])).view(np.uint64) == o["point_list_keys"]).all()
+    assert (_np(st["ranges"]).view(np.uint32) == o["ranges"]).all()
+    assert rel_err(_np(fw["color"]), o["out_color"]) < IMG_TOL
+    assert rel_err(_np(st["final_T"]), o["final_T"]) < IMG_TOL
+    # CPU libm expf differs from CUDA's in the last bit: a handful of threshold decisions may flip
+    assert (_np(st["n_contrib"]).view(np.uint32) != o["n_contrib"]).mean() < 1e-3
+
+
+@pytest.mark.parametrize("P,W,H,seed,kind,bg", CASES)
+def test_backward_vs_reference_cuda_and_oracle(gc, P, W, H, seed, kind, bg):
+    from oracle import raster_oracle as ro
+    from oracle import ref_cuda
+    inp = scene_inputs(P, W, H, seed=seed, kind=kind, bg=bg)
+    dL = smooth_dL(3, H, W, seed)
+    fw = gc.ours_forward(inp)
+    g = gc.ours_backward(fw, inp, dL)
+    o = oracle_forward(inp)
+    go = ro.rasterize_backward(o, dL)
+    keys = ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dscales", "dL_drotations"]
+    for k in keys:
+        assert rel_err(_np(g[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, ("oracle", k)
+    if ref_cuda.available():
+        ref, R, out, radii = gc.ref_forward(inp)
+        gr = ref.backward(gc.T(dL))
+        for k in keys:
+            assert rel_err(_np(g[k]).reshape(go[k].shape), _np(gr[k]).reshape(go[k].shape)) < GRAD_TOL, ("ref", k)
+            # the reference itself (float atomics) is held to the same bar against the fp64-accumulating oracle
+            assert rel_err(_np(gr[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, ("ref-vs-oracle", k)
+    # rows of culled Gaussians are written as zeros (outputs are not pre-zeroed by the caller)
+    culled = ~(fw["radii"] > 0)
+    for k in keys:
+        assert (g[k][culled] == 0).all()
+
+
+def test_backward_twice_gives_same_result(gc):
+    inp = scene_inputs(5000, 64, 64, seed=4)
+    dL = smooth_dL(3, 64, 64)
+    fw = gc.ours_forward(inp)
+    g1 = gc.ours_backward(fw, inp, dL)
+    g2 = gc.ours_backward(fw, inp, dL)
+    for k in g1:
+        assert rel_err(_np(g2[k]), _np(g1[k])) < 1e-5, k
+
+
+def test_sh_colours_and_precomputed_cov3d(gc):
+    """The raw-API branches train.py does not use (F3): SH -> RGB in the kernel, cov3D_precomp."""
+    from oracle import raster_oracle as ro
+    from oracle import ref_cuda
+    inp = scene_inputs(8000, 128, 96, seed=5)
+    for deg in (0, 1, 2, 3):
+        fw = gc.ours_forward(inp, use_sh=True, sh_degree=deg)
+        o = oracle_forward(inp, use_sh=True, sh_degree=deg)
+        assert fw["R"] == o["num_rendered"]
+        assert rel_err(_np(fw["color"]), o["out_color"]) < IMG_TOL
+        dL = smooth_dL(3, 96, 128, deg)
+        g = gc.ours_backward(fw, inp, dL)
+        go = ro.rasterize_backward(o, dL)
+        for k in ["dL_dsh", "dL_dmeans3D", "dL_dopacity", "dL_dscales", "dL_drotations"]:
+            assert rel_err(_np(g[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, (deg, k)
+        if ref_cuda.available():
+            ref, R, out, radii = gc.ref_forward(inp, use_sh=True, sh_degree=deg)
+            assert rel_err(_np(fw["color"]), _np(out)) < IMG_TOL
+    o = oracle_forward(inp)
+    fw = gc.ours_forward(inp, cov3D_precomp=o["cov3D"])
+    assert fw["R"] == o["num_rendered"] and (_np(fw["radii"]) == o["radii"]).all()
+    g = gc.ours_backward(fw, inp, smooth_dL(3, 96, 128))
+    o2 = oracle_forward(inp, cov3D_precomp=o["cov3D"])
+    go = ro.rasterize_backward(o2, smooth_dL(3, 96, 128))
+    assert rel_err(_np(g["dL_dcov3D"]), go["dL_dcov3D"]) < GRAD_TOL
+
+
+def test_single_channel_matches_luma_of_rgb(gc):
+    inp = scene_inputs(20_000, 160, 120, seed=6, bg=(0.1, 0.2, 0.3))
+    w = np.array([0.4124, 0.35758, 0.1804], np.float32)
+    fw3 = gc.ours_forward(inp)
+    inp1 = dict(inp)
+    inp1["colors"] = (inp["colors"] @ w)[:, None].astype(np.float32)
+    inp1["bg"] = np.array([inp["bg"] @ w], np.float32)
+    fw1 = gc.ours_forward(inp1)
+    luma = np.tensordot(w, _np(fw3["color"]), 1)
+    assert rel_err(_np(fw1["color"])[0], luma) < IMG_TOL
+    # dL/dcolour of the 1-channel render times w_k equals the RGB gradient under the luma seed
+    dY = smooth_dL(1, 120, 160)
+    g1 = gc.ours_backward(fw1, inp1, dY)
+    g3 = gc.ours_backward(fw3, inp, w[:, None, None] * dY)
+    assert rel_err(_np(g1["dL_dcolors"]) * w[None, :], _np(g3["dL_dcolors"])) < GRAD_TOL
+    for k in ["dL_dmeans3D", "dL_dopacity", "dL_dscales", "dL_drotations"]:
+        assert rel_err(_np(g1[k]), _np(g3[k])) < GRAD_TOL, k
+
+
+def test_edge_cases(gc):
+    # P == 0: all-zero image (rasterize_points.cu:68,81)
+    inp = scene_inputs(0, 64, 48, seed=7, bg=(0.3, 0.3, 0.3))
+    fw = gc.ours_forward(inp)
+    assert fw["R"] == 0 and (fw["color"] == 0).all() and fw["color"].shape == (3, 48, 64)
+    # every Gaussian culled: R == 0, image == background, zero gradients
+    inp = scene_inputs(100, 64, 48, seed=8, bg=(0.3, 0.6, 0.9))
+    inp["means3D"] = (inp["campos"][None, :] * 1.5).repeat(100, 0).astype(np.float32)
+    fw = gc.ours_forward(inp)
+    assert fw["R"] == 0 and (fw["radii"] == 0).all()
+    assert np.allclose(_np(fw["color"]), inp["bg"][:, None, None])
+    g = gc.ours_backward(fw, inp, smooth_dL(3, 48, 64))
+    assert all((v == 0).all() for v in g.values())
+    # one splat covering the whole frame (hundreds of tiles: cooperative emission path)
+    inp = scene_inputs(3, 320, 240, seed=9)
+    inp["scales"] = np.full((3, 3), 1.5, np.float32)
+    inp["means3D"] = np.zeros((3, 3), np.float32)
+    inp["means3D"][:, 0] = [0.0, 0.1, -0.1]
+    fw = gc.ours_forward(inp)
+    o = oracle_forward(inp)
+    assert fw["R"] == o["num_rendered"] == 3 * 20 * 15
+    assert rel_err(_np(fw["color"]), o["out_color"]) < IMG_TOL
+    # prefiltered with a culled point is an error (auxiliary.h:156-160)
+    inp = scene_inputs(10, 64, 48, seed=10)
+    inp["means3D"][0] = inp["campos"] * 1.5
+    with pytest.raises(RuntimeError):
+        gc.ours_forward(inp, prefiltered=True)
+
+
+def test_dropin_api_autograd_and_errors(gc):
+    from event_3dgs_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    inp = scene_inputs(4000, 96, 64, seed=11)
+    t = {k: gc.T(v) for k, v in inp.items() if isinstance(v, np.ndarray)}
+    settings = GaussianRasterizationSettings(image_height=64, image_width=96, tanfovx=inp["tanfovx"], tanfovy=inp["tanfovy"],
+                                             bg=t["bg"], scale_modifier=1.0, viewmatrix=t["viewmatrix"],
+                                             projmatrix=t["projmatrix"], sh_degree=0, campos=t["campos"],
+                                             prefiltered=False, debug=False)
+    rast = GaussianRasterizer(settings)
+    means = t["means3D"].clone().requires_grad_(True)
+    m2d = torch.zeros_like(means, requires_grad=True)
+    op = t["opacities"].clone().requires_grad_(True)
+    col = t["colors"].clone().requires_grad_(True)
+    sc = t["scales"].clone().requires_grad_(True)
+    rot = t["rotations"].clone().requires_grad_(True)
+    img, radii = rast(means3D=means, means2D=m2d, opacities=op, colors_precomp=col, scales=sc, rotations=rot)
+    assert img.shape == (3, 64, 96) and radii.dtype == torch.int32
+    dL = gc.T(smooth_dL(3, 64, 96))
+    (img * dL).sum().backward()
+    fw = gc.ours_forward(inp)
+    g = gc.ours_backward(fw, inp, smooth_dL(3, 64, 96))
+    assert rel_err(_np(means.grad), _np(g["dL_dmeans3D"])) < 1e-5
+    assert rel_err(_np(m2d.grad), _np(g["dL_dmeans2D"])) < 1e-5      # viewspace_points.grad (gaussian_model.py:406)
+    assert rel_err(_np(op.grad), _np(g["dL_dopacity"])) < 1e-5
+    assert (m2d.grad[:, 2] == 0).all()
+    vis = rast.markVisible(t["means3D"])
+    assert vis.dtype == torch.bool and vis.shape == (4000,)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        rast(means3D=means, means2D=m2d, opacities=op, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        rast(means3D=means, means2D=m2d, opacities=op, colors_precomp=col, scales=sc)
+    with pytest.raises(RuntimeError, match="means3D must have dimensions"):
+        rast(means3D=means.reshape(-1), means2D=m2d, opacities=op, colors_precomp=col, scales=sc, rotations=rot)
+
+
+def test_full_size_c3_properties(gc):
+    """BASELINE config c3 (1M Gaussians, 1280x720): size-independent properties."""
+    inp = scene_inputs(1_000_000, 1280, 720, seed=0)
+    fw = gc.ours_forward(inp)
+    st = gc.ours_state(fw, inp)
+    R = fw["R"]
+    assert R == int(st["tiles_touched"].long().sum())
+    keys = gc.sorted_keys(st, fw["radii"])
+    assert bool((keys[1:] >= keys[:-1]).all())                       # sortedness
+    # equal keys keep Gaussian-index order (stability)
+    eq = keys[1:] == keys[:-1]
+    pl = st["point_list"].long()
+    assert bool((pl[1:][eq] > pl[:-1][eq]).all())
+    # the multiset of instances is preserved: per-Gaussian instance counts equal tiles_touched
+    cnt = torch.bincount(pl, minlength=1_000_000)
+    assert torch.equal(cnt, st["tiles_touched"].long())
+    # ranges partition [0, R)
+    rg = st["ranges"].long()
+    lens = rg[:, 1] - rg[:, 0]
+    assert int(lens.sum()) == R
+    tcnt = torch.bincount(st["tile_ids"].long(), minlength=rg.shape[0])
+    assert torch.equal(tcnt, lens)
+    # linearity in colour and background: render(a*c1 + b*c2, a*bg1 + b*bg2) = a*render(c1,bg1) + b*render(c2,bg2)
+    inp2 = dict(inp)
+    inp2["colors"] = (0.25 * inp["colors"] + 0.5).astype(np.float32)
+    inp2["bg"] = np.array([0.5, 0.5, 0.5], np.float32)
+    fw2 = gc.ours_forward(inp2)
+    ones = dict(inp)
+    ones["colors"] = np.ones_like(inp["colors"])
+    ones["bg"] = np.array([1.0, 1.0, 1.0], np.float32)
+    fw1 = gc.ours_forward(ones)
+    assert rel_err(_np(fw2["color"]), 0.25 * _np(fw["color"]) + 0.5 * _np(fw1["color"])) < IMG_TOL
+    assert rel_err(_np(fw1["color"]), np.ones((3, 720, 1280), np.float32)) < IMG_TOL   # alpha + T = 1
+    g = gc.ours_backward(fw, inp, smooth_dL(3, 720, 1280))
+    assert all(bool(torch.isfinite(v).all()) for v in g.values())
