@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""bench.py -- train iters/sec of the Event-3DGS hot path (3 renders fwd + event loss + backward
+to leaf-parameter gradients per event view-pair) on synthetic scenes of the BASELINE.json shapes.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c3] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One JSON line on stdout (rank 0). See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "train_iters_per_sec"
+UNIT = "it/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--config", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--path", default="auto", choices=["auto", "dropin", "fused"])
+    ap.add_argument("--kind", default="trained", choices=["trained", "init"])
+    ap.add_argument("--P", type=int, default=None, help="override the number of Gaussians (debugging)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=25.0)
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------
+# shared: algorithmic bytes and workload description
+# --------------------------------------------------------------------------------------------
+def higher_msb(n):
+    msb, step = 16, 16
+    while step > 1:
+        step //= 2
+        msb = msb + step if (n >> msb) else msb - step
+    if n >> msb:
+        msb += 1
+    return msb
+
+
+def bytes_render(P, R, N, T):
+    """B_render of SURVEY.md 8d (reference algorithm, colours precomputed)."""
+    passes = -(-(32 + higher_msb(T)) // 8)
+    return 508 * P + (24 * passes + 108) * R + 40 * N + 32 * T
+
+
+def bytes_bwd_blend(P, R, N, T):
+    """Algorithmic bytes of ONE launch of the backward blend kernel: per instance the Gaussian id
+    (4) + xy (8) + conic/opacity (16) + colour (12); per pixel final_T, n_contrib, dL/dpixel (20);
+    per tile its range (8); per Gaussian the 9 accumulated gradients (36)."""
+    return 40 * R + 20 * N + 8 * T + 36 * P
+
+
+def workload(cfg, name, kind, pairs):
+    return {"workload": "%s: %d Gaussians, %dx%d, %s, event view-pair = 3 renders fwd + event loss%s + bwd" % (
+        name, cfg["P"], cfg["W"], cfg["H"], "RGB SH deg %d" % cfg["sh_degree"] if cfg["sh_degree"] else "gray SH deg 0",
+        " + blurry L1" if cfg["deblur"] else ""),
+        "gaussians": cfg["P"], "width": cfg["W"], "height": cfg["H"], "sh_degree": cfg["sh_degree"],
+        "deblur": bool(cfg["deblur"]), "params": kind, "pairs_per_step": pairs,
+        "l2": "inputs of one step (>150 MB of Gaussian state and instance lists at c3) exceed the 126 MB L2; "
+              "a different view triplet is rendered every step"}
+
+
+# --------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md recipe)
+# --------------------------------------------------------------------------------------------
+class Clocks:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown," \
+        "clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                mx = float(f[2])
+                if t0 - 0.05 <= ts <= t1 + 0.15:
+                    sm.append(float(f[1]))
+                    for n, v in zip(names, f[4:8]):
+                        if v.lower().startswith("active"):
+                            reasons.add(n)
+            except ValueError:
+                continue
+        if not sm:          # region shorter than the sampling period: take everything we saw
+            for ts, line in self.rows:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    sm.append(float(f[1]))
+                except Exception:
+                    pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the oracle (C restatement, OpenMP over all host cores) on a bounded sample
+# --------------------------------------------------------------------------------------------
+def cpu_iteration(scene, triplet, rows, deblur):
+    """One event iteration on the CPU oracle; the blend loops only cover the first `rows` pixel
+    rows. Returns (seconds for the per-Gaussian/binning stages, seconds for the blends)."""
+    from event_3dgs_b200 import synthetic as syn
+    from oracle import loss_oracle as lo
+    from oracle import raster_oracle as ro
+    a = syn.activate(scene["gaussians"])
+    cfg = scene["cfg"]
+    W, H = cfg["W"], cfg["H"]
+    L = ro.lib()
+    sts, t_geo, t_blend = [], 0.0, 0.0
+    colors = np.clip(a["shs"][:, 0, :] * 0.28209479177387814 + 0.5, 0, None).astype(np.float32)   # SH deg 0 colours
+    bg = np.zeros(3, np.float32)
+    for v in triplet:
+        cam = scene["cameras"][v]
+        t0 = time.perf_counter()
+        L.orc_set_pixel_window(0, 0)
+        st = ro.rasterize_forward(a["means3D"], a["opacities"], cam["world_view_transform"], cam["full_proj_transform"],
+                                  cam["camera_center"], bg, W, H, cam["tanfovx"], cam["tanfovy"], scales=a["scales"],
+                                  rotations=a["rotations"], colors_precomp=colors)
+        t1 = time.perf_counter()
+        L.orc_set_pixel_window(0, rows * W)
+        feat = st["colors_precomp"]
+        L.orc_render_forward(3, st["gx"], st["gy"], ro._p(st["ranges"]), ro._p(st["point_list"]), W, H, ro._p(st["means2D"]),
+                             ro._p(feat), ro._p(st["conic_opacity"]), ro._p(st["final_T"]), ro._p(st["n_contrib"]),
+                             ro._p(bg), ro._p(st["out_color"]))
+        t2 = time.perf_counter()
+        t_geo += t1 - t0
+        t_blend += t2 - t1
+        sts.append(st)
+    t0 = time.perf_counter()
+    gt = scene["gt"]
+    loss, gr = lo.event_loss(sts[0]["out_color"], sts[1]["out_color"], sts[2]["out_color"], gt["event_now"],
+                             gt["event_next"], gt["intensity"], 0.17, gt["blurry"] if deblur else None)
+    t_geo += time.perf_counter() - t0
+    for st, k in zip(sts, ("image", "image_now", "image_next")):
+        t0 = time.perf_counter()
+        g = ro.rasterize_backward(st, gr[k].astype(np.float32))      # honours the pixel window
+        t_blend += time.perf_counter() - t0
+        del g
+    L.orc_set_pixel_window(0, 0x7fffffff)
+    return t_geo, t_blend
+
+
+def cpu_arm(scene, steps, warmup, budget_s):
+    """Times the oracle; every step is the full per-Gaussian work plus a band of pixel rows of
+    the blends, extrapolated to the whole frame (blend cost is proportional to rows)."""
+    H = scene["cfg"]["H"]
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    deblur = scene["cfg"]["deblur"]
+    probe_rows = max(16, (H // 16 // 8) * 16)
+    tg, tb = cpu_iteration(scene, (3, 3, 4), probe_rows, deblur)          # calibration (also warms caches)
+    per_row = tb / probe_rows
+    per_step_budget = budget_s / max(1, steps + max(0, warmup - 1))
+    rows = int(max(16, min(H, ((per_step_budget - tg) / max(per_row, 1e-9)) // 16 * 16)))
+    for _ in range(max(0, warmup - 1)):
+        cpu_iteration(scene, (3, 3, 4), rows, deblur)
+    est = []
+    for s in range(steps):
+        v = 2 + (7 * s) % 80
+        tg, tb = cpu_iteration(scene, (v, v, v + 1), rows, deblur)
+        est.append(tg + tb * (H / float(rows)))
+    t_iter = float(np.mean(est))
+    sample = "C oracle (OpenMP, %d threads): full projection/binning of all Gaussians for 3 views + event loss, " \
+             "blend fwd+bwd over the first %d of %d pixel rows, extrapolated to the frame; %d steps" % (cores, rows, H, steps)
+    return 1.0 / t_iter, t_iter, cores, sample
+
+
+# --------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    from event_3dgs_b200 import synthetic as syn
+    cfg_name = args.config
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        # the reference's own algorithm on the host cores (oracle port), rank 0 only
+        if rank != 0:
+            return
+        scene = syn.make_scene(cfg_name, kind=args.kind, P=args.P)
+        v, t_iter, cores, sample = cpu_arm(scene, max(1, args.steps), max(1, args.warmup), 150.0)
+        line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * t_iter, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload(scene["cfg"], cfg_name, args.kind, 1),
+                "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from event_3dgs_b200 import _lib, pipeline as pl
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+
+    scene = syn.make_scene(cfg_name, kind=args.kind, P=args.P)
+    cfg = scene["cfg"]
+    W, H, P = cfg["W"], cfg["H"], cfg["P"]
+    N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    deblur = cfg["deblur"]
+    pc = pl.GaussianParams(scene["gaussians"], dev)
+    cams = [pl.make_camera(c, dev) for c in scene["cameras"]]
+    gt_host = {k: torch.as_tensor(v).pin_memory() for k, v in scene["gt"].items()}
+    gt_dev = {k: v.to(dev) for k, v in gt_host.items()}
+    bg = torch.zeros(3, device=dev)
+    c_param = torch.nn.Parameter(torch.tensor(0.17, device=dev))
+    leaves = pc.leaves() + [c_param]
+
+    use_fused = False
+    if args.path in ("auto", "fused"):
+        try:
+            from event_3dgs_b200 import fused  # noqa: F401
+            use_fused = True
+        except ImportError:
+            if args.path == "fused":
+                raise
+    path_name = "fused" if use_fused else "dropin"
+
+    def view_of(step):
+        # every rank renders its own view-pair of the step (pair b of a step -> rank b mod G)
+        v = 2 + (7 * (step * world + rank)) % 80
+        return v
+
+    record_R = []
+
+    def iteration(step, gt, sync_grads=True):
+        v = view_of(step)
+        for p in leaves:
+            p.grad = None
+        if use_fused:
+            loss = fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur)
+        else:
+            loss, pkg = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur)
+            loss.backward()
+        if world > 1 and sync_grads:
+            from event_3dgs_b200 import parallel
+            parallel.allreduce_gradients(leaves, world)
+        return loss
+
+    def timed(fn, steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record()
+        for s in range(steps):
+            fn(s)
+        e1.record()
+        torch.cuda.synchronize()
+        w1 = time.time()
+        if world > 1:
+            dist.barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, w0, w1
+
+    # ---- warm-up (also grows the caching allocator to its steady state) ----
+    for s in range(max(3, args.warmup)):
+        iteration(s, gt_dev)
+    torch.cuda.synchronize()
+
+    # ---- (1) resident run: inputs already in HBM ----
+    clocks = Clocks(local_rank) if rank == 0 else None
+    _lib.profile_enable(["render_bwd"])
+    _lib.profile_read(reset=True)
+    l0 = _lib.lib().e3_kernel_launches()
+    ms, w0, w1 = timed(lambda s: iteration(args.warmup + s, gt_dev), args.steps)
+    launches = _lib.lib().e3_kernel_launches() - l0
+    prof = _lib.profile_read(reset=True)
+    _lib.profile_enable([])
+    clk = clocks.stop(w0, w1) if clocks else None
+    ms_per_step = ms / args.steps
+    value = world * 1e3 / ms_per_step
+
+    # ---- (2) end to end through the public API with host buffers ----
+    h2d = sum(v.numel() * v.element_size() for k, v in gt_host.items() if deblur or k != "blurry")
+    cam_bytes = 3 * (16 + 16 + 3) * 4
+
+    def e2e_step(s):
+        gt = {k: v.to(dev, non_blocking=True) for k, v in gt_host.items() if deblur or k != "blurry"}
+        loss = iteration(args.warmup + s, gt)
+        return float(loss.detach().cpu())           # device -> host read of the step's result
+
+    for s in range(2):
+        e2e_step(s)
+    ms_e2e, _, _ = timed(e2e_step, args.steps)
+    e2e_value = world * 1e3 / (ms_e2e / args.steps)
+
+    # ---- (3) per-stage breakdown and workload statistics (untimed pass) ----
+    _lib.profile_enable(_lib.STAGES)
+    _lib.profile_read(reset=True)
+    nprof = 3
+    for s in range(nprof):
+        iteration(args.warmup + s, gt_dev, sync_grads=False)
+    torch.cuda.synchronize()
+    stages = {k: v[0] / nprof for k, v in _lib.profile_read(reset=True).items()}
+    _lib.profile_enable([])
+    # measured num_rendered of the three renders of one step
+    Rs = []
+    with torch.no_grad():
+        v = view_of(args.warmup)
+        for cam in (cams[v], cams[v], cams[v + 1]):
+            pkg = pl.render(cam, pc, pl.PIPE, bg)
+            Rs.append(int(last_num_rendered()))
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload(cfg, cfg_name, args.kind, world)}
+    line["config"]["path"] = path_name
+    line["config"]["num_rendered"] = Rs
+    line["mpix_per_sec"] = value * 3 * N / 1e6
+    line["e2e"] = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d + cam_bytes), "d2h_bytes_per_step": 4,
+                   "ms_per_step": ms_e2e / args.steps}
+    line["gpu_launches"] = int(launches)
+    line["clocks"] = clk
+    # roofline of the dominant kernel (backward blend), timed live with CUDA events in run (1)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    if "render_bwd" in prof and prof["render_bwd"][1] > 0:
+        t_ms, n = prof["render_bwd"]
+        per_launch_ms = t_ms / n
+        algo = float(np.mean([bytes_bwd_blend(P, r, N, T) for r in Rs]))
+        ach = algo / (per_launch_ms * 1e-3) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": "render_bwd_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                            "frac": ach / peak, "traffic": None, "launch_ms": per_launch_ms, "launches": int(n),
+                            "algorithmic_bytes_per_launch": algo,
+                            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                            "note": "the blend kernels are issue/latency bound, not HBM bound; see DESIGN.md"}
+    b_iter = sum(bytes_render(P, r, N, T) for r in Rs) + 108 * N + (24 * N if deblur else 0)
+    line["iter_roofline"] = {"algorithmic_bytes": b_iter, "achieved_gbs": b_iter / (ms_per_step * 1e-3) / 1e9,
+                             "frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak}
+    line["stages_ms_per_iter"] = stages
+
+    if rank == 0 and world == 1:
+        # reference CUDA build (oracle/_ref) on the same tensors, same timing window
+        if not args.no_ref_cuda:
+            try:
+                line["ref_cuda"] = ref_cuda_leg(pc, cams, gt_dev, c_param, bg, deblur, args, view_of, timed, leaves)
+                line["ref_cuda"]["speedup"] = value / line["ref_cuda"]["value"]
+            except Exception as ex:   # the checker is optional for the number
+                line["ref_cuda"] = {"unavailable": repr(ex)[:200]}
+        if not args.no_cpu_baseline:
+            v, t_iter, cores, sample = cpu_arm(scene, 2, 1, args.cpu_budget_s)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def last_num_rendered():
+    from event_3dgs_b200 import rasterizer
+    return rasterizer.LAST_NUM_RENDERED
+
+
+def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves):
+    """The unmodified reference rasterizer (oracle/_ref) under the reference's own render() /
+    loss flow (PyTorch SH + activations + loss), timed exactly like run (1)."""
+    import torch
+    from event_3dgs_b200 import pipeline as pl
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        return {"unavailable": "oracle/_ref/libref_dgr.so not built"}
+
+    def render_ref(cam, pc_, pipe, bg_, **kw):
+        return pl.render(cam, pc_, pipe, bg_, rasterizer_cls=ref_cuda.RefGaussianRasterizer)
+
+    def it(s):
+        v = view_of(args.warmup + s)
+        for p in leaves:
+            p.grad = None
+        loss, _ = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur, render_fn=render_ref)
+        loss.backward()
+
+    for s in range(3):
+        it(s)
+    steps = max(3, min(args.steps, 10))
+    ms, _, _ = timed(it, steps)
+    return {"value": 1e3 / (ms / steps), "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
+            "what": "reference diff-gaussian-rasterization sources compiled for sm_100a (oracle/_ref) + PyTorch SH/loss"}
+
+
+if __name__ == "__main__":
+    main()

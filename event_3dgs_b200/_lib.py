@@ -28,6 +28,9 @@ SIGNATURES = {
                                    _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
+    "e3_profile_enable": (_i, [ctypes.c_uint]),
+    "e3_kernel_launches": (ctypes.c_ulonglong, []),
+    "e3_profile_read": (_i, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), _i]),
     "e3_geometry_ptr": (_vp, [_vp, _i, _i]),
     "e3_binning_ptr": (_vp, [_vp, _i, _i]),
     "e3_image_ptr": (_vp, [_vp, _i, _i, _i]),
@@ -63,3 +66,24 @@ def check(code):
     if code != 0:
         msg = lib().e3_error_string(code)
         raise RuntimeError(msg.decode() if msg else "event3dgs error %d" % code)
+
+
+STAGES = ["preprocess_fwd", "depth_sort", "offsets_scan", "emit", "tile_sort", "tile_ranges", "render_fwd",
+          "render_bwd", "preprocess_bwd", "event_loss", "dist2", "activate"]
+NUM_STAGES = 16
+
+
+def profile_enable(names):
+    """Bracket the named stages with CUDA events on the launching stream (names: see STAGES)."""
+    mask = 0
+    for n in names:
+        mask |= 1 << STAGES.index(n)
+    check(lib().e3_profile_enable(mask))
+
+
+def profile_read(reset=True):
+    """{stage: (total_ms, launches)} since the last reset."""
+    ms = (ctypes.c_double * NUM_STAGES)()
+    cnt = (ctypes.c_longlong * NUM_STAGES)()
+    check(lib().e3_profile_read(ms, cnt, int(reset)))
+    return {n: (ms[i], cnt[i]) for i, n in enumerate(STAGES) if cnt[i]}

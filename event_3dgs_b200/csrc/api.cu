@@ -5,6 +5,10 @@
 #include "../../include/event3dgs.h"
 
 #include <cstdio>
+#include <mutex>
+#include <vector>
+
+unsigned long long g_e3_launches = 0;
 
 namespace {
 
@@ -34,8 +38,39 @@ E3Frame make_frame(int P, int D, int M, int C, int W, int H, float tan_fovx, flo
 }
 
 #define E3_CHECK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (int)e__; } while (0)
+
+// ---- optional per-stage device timing (CUDA events on the launching stream) ----
+struct ProfSpan { int stage; cudaEvent_t a, b; };
+unsigned g_prof_mask = 0;
+std::vector<ProfSpan> g_prof_open;
+std::vector<cudaEvent_t> g_prof_pool;
+double g_prof_ms[E3_NUM_STAGES];
+long long g_prof_n[E3_NUM_STAGES];
+std::mutex g_prof_mu;
+
+cudaEvent_t prof_event()
+{
+	cudaEvent_t e;
+	if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+	cudaEventCreate(&e);
+	return e;
+}
+
+struct ProfScope {
+	int stage; cudaStream_t st; bool on; cudaEvent_t a;
+	ProfScope(int stage_, cudaStream_t st_) : stage(stage_), st(st_), on((g_prof_mask >> stage_) & 1u)
+	{
+		if (on) { std::lock_guard<std::mutex> l(g_prof_mu); a = prof_event(); cudaEventRecord(a, st); }
+	}
+	~ProfScope()
+	{
+		if (on) { std::lock_guard<std::mutex> l(g_prof_mu); cudaEvent_t b = prof_event(); cudaEventRecord(b, st); g_prof_open.push_back({ stage, a, b }); }
+	}
+};
+
 // debug mode: sync-and-check after every stage, like CHECK_CUDA (auxiliary.h:166-173)
-#define E3_STAGE(expr) do { E3_CHECK(expr); if (debug) { E3_CHECK(cudaStreamSynchronize(st)); } } while (0)
+#define E3_STAGE(id, expr) do { cudaError_t es__; { ProfScope ps__(id, st); es__ = (expr); } \
+	if (es__ != cudaSuccess) return (int)es__; if (debug) { E3_CHECK(cudaStreamSynchronize(st)); } } while (0)
 
 }  // namespace
 
@@ -112,15 +147,15 @@ int e3_rasterize_forward(
 	E3ImageState im = E3ImageState::carve(ibuf, N, T);
 
 	E3_CHECK(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), st));
-	E3_STAGE(e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+	E3_STAGE(E3_STAGE_PREPROCESS_FWD, e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
 		viewmatrix, projmatrix, cam_pos, prefiltered != 0, radii, g, st));
 
 	// depth order of the Gaussians (culled ones carry key 0xffffffff and emit nothing)
 	int dres = 0;
-	E3_STAGE(e3_radix_sort_pairs(g.dkey, g.dval, (size_t)P, 32, g.sort_counts, g.scan_tmp, &dres, st));
+	E3_STAGE(E3_STAGE_DEPTH_SORT, e3_radix_sort_pairs(g.dkey, g.dval, (size_t)P, 32, g.sort_counts, g.scan_tmp, 0, &dres, st));
 	const uint32_t* order = g.dval[dres];
 	// instance offsets in depth order; grand total = num_rendered
-	E3_STAGE(e3_exclusive_scan_u32(g.tiles_touched, order, g.offsets, (size_t)P, g.scan_tmp,
+	E3_STAGE(E3_STAGE_OFFSETS_SCAN, e3_exclusive_scan_u32(g.tiles_touched, order, g.offsets, (size_t)P, g.scan_tmp,
 		reinterpret_cast<uint32_t*>(g.flags), st));
 
 	int h_flags[2] = { 0, 0 };
@@ -134,16 +169,15 @@ int e3_rasterize_forward(
 	if (!bbuf) return E3_ERR_ALLOC_FAILED;
 	E3BinState b = E3BinState::carve(bbuf, (size_t)R);
 
-	E3_STAGE(e3_launch_emit_instances(P, order, g.offsets, g.tiles_touched, g.rect, f.gx, b.tkey[0], b.val[0], st));
+	// emit into the ping-pong slot from which the tile sort ends in slot 0, where backward looks
+	const int tile_bits = (int)higher_msb((uint32_t)T);
+	const int s0 = (R > 0) ? (e3_radix_passes(tile_bits) & 1) : 0;
+	E3_STAGE(E3_STAGE_EMIT, e3_launch_emit_instances(P, order, g.offsets, g.tiles_touched, g.rect, f.gx, b.tkey[s0], b.val[s0], st));
 	int bres = 0;
-	E3_STAGE(e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, (int)higher_msb((uint32_t)T), b.sort_counts, b.scan_tmp, &bres, st));
-	if (bres != 0) {
-		// keep the sorted lists in slot 0 so that backward finds them without extra state
-		E3_CHECK(cudaMemcpyAsync(b.tkey[0], b.tkey[1], (size_t)R * 4, cudaMemcpyDeviceToDevice, st));
-		E3_CHECK(cudaMemcpyAsync(b.val[0], b.val[1], (size_t)R * 4, cudaMemcpyDeviceToDevice, st));
-	}
-	E3_STAGE(e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
-	E3_STAGE(e3_launch_render_forward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
+	E3_STAGE(E3_STAGE_TILE_SORT, e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, tile_bits, b.sort_counts, b.scan_tmp, s0, &bres, st));
+	if (bres != 0) return E3_ERR_BAD_ARGUMENT;
+	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
+	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
 	return 0;
 }
 
@@ -175,10 +209,10 @@ int e3_rasterize_backward(
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
 	if (R > 0) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
-		E3_STAGE(e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
-	E3_STAGE(e3_launch_preprocess_backward(f, means3D, radii, shs, scales, rotations, cov3D_precomp, viewmatrix,
+	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, means3D, radii, shs, scales, rotations, cov3D_precomp, viewmatrix,
 		projmatrix, campos, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh,
 		dL_dscale, dL_drot, st));
 	return 0;
@@ -192,6 +226,38 @@ int e3_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 	if (P == 0) return 0;
 	if (!means3D || !viewmatrix || !present) return E3_ERR_BAD_ARGUMENT;
 	E3_CHECK(e3_launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream));
+	return 0;
+}
+
+unsigned long long e3_kernel_launches(void) { return g_e3_launches; }
+
+int e3_profile_enable(unsigned stage_mask)
+{
+	std::lock_guard<std::mutex> l(g_prof_mu);
+	g_prof_mask = stage_mask;
+	return 0;
+}
+
+int e3_profile_read(double* ms_sum, long long* count, int reset)
+{
+	std::lock_guard<std::mutex> l(g_prof_mu);
+	for (const ProfSpan& sp : g_prof_open) {
+		cudaError_t e = cudaEventSynchronize(sp.b);
+		if (e != cudaSuccess) return (int)e;
+		float ms = 0.f;
+		e = cudaEventElapsedTime(&ms, sp.a, sp.b);
+		if (e != cudaSuccess) return (int)e;
+		g_prof_ms[sp.stage] += ms;
+		g_prof_n[sp.stage] += 1;
+		g_prof_pool.push_back(sp.a);
+		g_prof_pool.push_back(sp.b);
+	}
+	g_prof_open.clear();
+	for (int i = 0; i < E3_NUM_STAGES; i++) {
+		if (ms_sum) ms_sum[i] = g_prof_ms[i];
+		if (count) count[i] = g_prof_n[i];
+		if (reset) { g_prof_ms[i] = 0.0; g_prof_n[i] = 0; }
+	}
 	return 0;
 }
 

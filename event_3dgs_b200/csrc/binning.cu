@@ -243,13 +243,14 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 	scan_reduce_kernel<<<(unsigned)nb, E3_SCAN_THREADS, 0, st>>>(in, idx, n, tmp);
 	scan_sums_kernel<<<1, E3_SCAN_THREADS, 0, st>>>(tmp, nb, total);
 	scan_down_kernel<<<(unsigned)nb, E3_SCAN_THREADS, 0, st>>>(in, idx, n, tmp, out);
+	g_e3_launches += 3;
 	return cudaGetLastError();
 }
 
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int* result_buf, cudaStream_t st)
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st)
 {
-	int cur = 0;
+	int cur = start_buf;
 	if (n > 0 && end_bit > 0) {
 		const int npass = (end_bit + 7) / 8;
 		const size_t nblk = e3_sort_blocks(n);
@@ -265,6 +266,7 @@ cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, 
 			if (e != cudaSuccess) return e;
 			radix_scatter_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1],
 				vals[cur ^ 1], n, lo, mask, counts, (uint32_t)nblk);
+			g_e3_launches += 2;
 			cur ^= 1;
 			lo += nb;
 		}
@@ -278,6 +280,7 @@ cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_
 	cudaStream_t st)
 {
 	emit_instances_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tiles_touched, rect, gx, tkeys, vals);
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
@@ -285,6 +288,6 @@ cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges
 {
 	cudaError_t e = cudaMemsetAsync(ranges, 0, T * sizeof(uint2), st);
 	if (e != cudaSuccess) return e;
-	if (R > 0) tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges);
+	if (R > 0) { tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges); g_e3_launches += 1; }
 	return cudaGetLastError();
 }

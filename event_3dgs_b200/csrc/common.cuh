@@ -112,6 +112,9 @@ struct E3BinState {
 	}
 };
 
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+extern unsigned long long g_e3_launches;
+
 // ---- internal launchers (defined in the .cu files) ----
 struct E3Frame {
 	int P, D, M, C, W, H, gx, gy;
@@ -134,10 +137,12 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 // out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (optional, device) = sum of all
 cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint32_t* out,
 	size_t n, uint32_t* tmp, uint32_t* total, cudaStream_t st);
-// Stable LSD radix sort of (key,val) pairs over key bits [0,end_bit). Returns the index (0/1)
-// of the ping-pong buffer that holds the result in *result_buf.
+// Stable LSD radix sort of (key,val) pairs over key bits [0,end_bit). The input is read from
+// ping-pong buffer `start_buf`; *result_buf receives the index (0/1) of the buffer that holds
+// the result. e3_radix_passes() tells how many passes (buffer flips) that takes.
+static inline int e3_radix_passes(int end_bit) { return (end_bit + 7) / 8; }
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int* result_buf, cudaStream_t st);
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st);
 cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_t* offsets,
 	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals,
 	cudaStream_t st);

@@ -519,6 +519,7 @@ cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const f
 	g.clamped, g.tiles_touched, g.rect, g.dkey[0], g.dval[0], g.acc, g.flags)
 	if (f.C == 1) LAUNCH(1); else LAUNCH(3);
 #undef LAUNCH
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
@@ -526,6 +527,7 @@ cudaError_t e3_launch_mark_visible(int P, const float* means3D, const float* vie
 	uint8_t* present, cudaStream_t st)
 {
 	mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, viewmatrix, present);
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
@@ -543,5 +545,6 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	dL_dscale, dL_drot)
 	if (f.C == 1) LAUNCH(1); else LAUNCH(3);
 #undef LAUNCH
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }

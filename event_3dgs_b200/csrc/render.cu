@@ -265,6 +265,7 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, cons
 	const dim3 grid(f.gx, f.gy, 1);
 	if (f.C == 1) render_fwd_kernel<1><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
 	else render_fwd_kernel<3><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
@@ -275,5 +276,6 @@ cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, con
 	const dim3 grid(f.gx, f.gy, 1);
 	if (f.C == 1) render_bwd_kernel<1><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
 	else render_bwd_kernel<3><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
+	g_e3_launches += 1;
 	return cudaGetLastError();
 }

@@ -14,6 +14,8 @@ import torch.nn as nn
 
 from . import _lib
 
+LAST_NUM_RENDERED = 0     # R of the most recent forward (bench.py reads it for the roofline)
+
 # ---- workspace callbacks (replace resizeFunctional, rasterize_points.cu:27-33) ----
 _slots = {}
 
@@ -85,6 +87,8 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
     geom, binning, img = _slots.get(1, empty), _slots.get(2, empty), _slots.get(3, empty)
     _slots.clear()
     _lib.check(code)
+    global LAST_NUM_RENDERED
+    LAST_NUM_RENDERED = R.value
     return R.value, out_color, radii, geom, binning, img
 
 

@@ -130,6 +130,23 @@ E3_API int e3_rasterize_backward(
 E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,
 	const float* projmatrix, uint8_t* present, void* stream);
 
+/* Optional per-stage device timing, used by bench.py for the roofline of the dominant kernel.
+ * No counterpart in the reference (it only brackets the whole iteration with two CUDA events,
+ * train.py:64-65,95,299). While bit `s` of stage_mask is set, every launch group of stage `s` is
+ * bracketed by two cudaEvents recorded on the call's stream; e3_profile_read() waits for the
+ * recorded events, adds their elapsed milliseconds to per-stage sums and returns sums and launch
+ * counts (arrays of E3_NUM_STAGES). Process-global and meant for one host thread. */
+enum {
+	E3_STAGE_PREPROCESS_FWD = 0, E3_STAGE_DEPTH_SORT = 1, E3_STAGE_OFFSETS_SCAN = 2, E3_STAGE_EMIT = 3,
+	E3_STAGE_TILE_SORT = 4, E3_STAGE_TILE_RANGES = 5, E3_STAGE_RENDER_FWD = 6, E3_STAGE_RENDER_BWD = 7,
+	E3_STAGE_PREPROCESS_BWD = 8, E3_STAGE_EVENT_LOSS = 9, E3_STAGE_DIST2 = 10, E3_STAGE_ACTIVATE = 11,
+	E3_NUM_STAGES = 16
+};
+E3_API int e3_profile_enable(unsigned stage_mask);
+/* Number of CUDA kernels launched by this library since it was loaded (no reference counterpart). */
+E3_API unsigned long long e3_kernel_launches(void);
+E3_API int e3_profile_read(double* ms_sum_host, long long* count_host, int reset);
+
 /* Test / inspection hooks: device pointers into the opaque buffers of a finished forward.
  * `which` (geometry): 0 depths f32[P], 1 packed records float4[3P] ({x,y,conic.x,conic.y},
  *   {conic.z,opacity,c0,c1},{c2,-,-,-}), 2 cov3D f32[6P], 3 tiles_touched u32[P],

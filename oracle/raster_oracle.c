@@ -333,6 +333,11 @@ void orc_identify_tile_ranges(int L, const uint64_t* keys, uint32_t* ranges)
 	}
 }
 
+/* Timing aid for bench.py's bounded CPU sample: restrict both blend loops to the pixel window
+ * [begin, end) (row-major pixel ids). Default = whole image. Not used by any parity test. */
+static int g_pix_begin = 0, g_pix_end = 0x7fffffff;
+void orc_set_pixel_window(int begin, int end) { g_pix_begin = begin; g_pix_end = end; }
+
 /* forward.cu:261-374 (renderCUDA). One pixel at a time: the per-pixel result does not depend on
  * the block's batching. C = channels of `features` (3 in the reference, config.h:15; 1 is the
  * luma rewrite of SURVEY.md section 7). */
@@ -341,8 +346,9 @@ void orc_render_forward(int C, int gridx, int gridy, const uint32_t* ranges, con
 	float* final_T, uint32_t* n_contrib, const float* bg, float* out_color)
 {
 	(void)gridy;
+	const int pb = g_pix_begin > 0 ? g_pix_begin : 0, pe = g_pix_end < W * H ? g_pix_end : W * H;
 #pragma omp parallel for schedule(dynamic, 64)
-	for (int pix_id = 0; pix_id < W * H; pix_id++) {
+	for (int pix_id = pb; pix_id < pe; pix_id++) {
 		int px = pix_id % W, py = pix_id / W;
 		uint32_t tile = (uint32_t)(py / BLOCK_Y) * gridx + (px / BLOCK_X);
 		uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];
@@ -385,8 +391,9 @@ void orc_render_backward(int C, int P, int gridx, int gridy, const uint32_t* ran
 	(void)gridy;
 	double* acc = (double*)calloc((size_t)P * (6 + C), sizeof(double));
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+	const int pb = g_pix_begin > 0 ? g_pix_begin : 0, pe = g_pix_end < W * H ? g_pix_end : W * H;
 #pragma omp parallel for schedule(dynamic, 64)
-	for (int pix_id = 0; pix_id < W * H; pix_id++) {
+	for (int pix_id = pb; pix_id < pe; pix_id++) {
 		int px = pix_id % W, py = pix_id / W;
 		uint32_t tile = (uint32_t)(py / BLOCK_Y) * gridx + (px / BLOCK_X);
 		uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];

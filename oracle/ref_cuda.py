@@ -120,3 +120,47 @@ class RefRasterizer:
             if rc != 0:
                 raise RuntimeError("ref_copy_state failed: %d" % rc)
         return out
+
+
+# ---- autograd wrapper with the reference's python surface (for the reference-CUDA timing leg) ----
+class _RefRasterize(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, colors_precomp, opacities, scales, rotations, settings, handle):
+        s = settings
+        R, out, radii = handle.forward(means3D.contiguous(), opacities.contiguous(), s.viewmatrix, s.projmatrix, s.campos,
+                                       s.bg, s.image_width, s.image_height, s.tanfovx, s.tanfovy, scales=scales.contiguous(),
+                                       rotations=rotations.contiguous(), colors_precomp=colors_precomp.contiguous(),
+                                       scale_modifier=s.scale_modifier)
+        ctx.handle = handle
+        ctx.saved_args = handle.args
+        ctx.R = R
+        ctx.mark_non_differentiable(radii)
+        return out, radii
+
+    @staticmethod
+    def backward(ctx, grad_out, _):
+        h = ctx.handle
+        h.args, h.R = ctx.saved_args, ctx.R
+        g = h.backward(grad_out)
+        return (g["dL_dmeans3D"], g["dL_dmeans2D"], g["dL_dcolors"], g["dL_dopacity"], g["dL_dscales"],
+                g["dL_drotations"], None, None)
+
+
+class RefGaussianRasterizer:
+    """GaussianRasterizer-shaped front of the reference CUDA build. The reference keeps the three
+    state buffers of every forward alive until its backward, so each live forward needs its own
+    handle: `pool` hands them out round-robin (3 renders per event iteration)."""
+    pool = []
+    cursor = 0
+
+    def __init__(self, raster_settings):
+        self.raster_settings = raster_settings
+
+    def __call__(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                 cov3D_precomp=None):
+        cls = RefGaussianRasterizer
+        while len(cls.pool) < 4:
+            cls.pool.append(RefRasterizer())
+        h = cls.pool[cls.cursor % len(cls.pool)]
+        cls.cursor += 1
+        return _RefRasterize.apply(means3D, means2D, colors_precomp, opacities, scales, rotations, self.raster_settings, h)

@@ -39,10 +39,12 @@ def oracle_forward(inp, use_sh=False, sh_degree=0, cov3D_precomp=None):
                                 inp["bg"], inp["W"], inp["H"], inp["tanfovx"], inp["tanfovy"], **kw)
 
 
-def rel_err(a, b):
-    """max |a-b| / max |b| -- the 'rel' of BASELINE.json's tolerances (relative to the array scale)."""
+def rel_err(a, b, floor=0.0):
+    """max |a-b| / max(max |b|, floor) -- the 'rel' of BASELINE.json's tolerances (relative to the
+    array scale). `floor` guards arrays that are mathematically zero (e.g. dL/drotation of
+    isotropic Gaussians), where only rounding noise is left to compare."""
     a = np.asarray(a, np.float64)
     b = np.asarray(b, np.float64)
     d = np.abs(a - b).max() if a.size else 0.0
-    s = np.abs(b).max() if b.size else 0.0
+    s = max(np.abs(b).max() if b.size else 0.0, floor)
     return d / s if s > 0 else d

@@ -91,15 +91,19 @@ def test_backward_vs_reference_cuda_and_oracle(gc, P, W, H, seed, kind, bg):
     o = oracle_forward(inp)
     go = ro.rasterize_backward(o, dL)
     keys = ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dscales", "dL_drotations"]
+    # dL/drotation vanishes identically for isotropic Gaussians (the init-like case): measure it
+    # against the scale of its sibling gradient instead of against rounding noise
+    fl = {k: 0.0 for k in keys}
+    fl["dL_drotations"] = 1e-3 * float(np.abs(go["dL_dscales"]).max()) * float(np.abs(inp["scales"]).max())
     for k in keys:
-        assert rel_err(_np(g[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, ("oracle", k)
+        assert rel_err(_np(g[k]).reshape(go[k].shape), go[k], fl[k]) < GRAD_TOL, ("oracle", k)
     if ref_cuda.available():
         ref, R, out, radii = gc.ref_forward(inp)
         gr = ref.backward(gc.T(dL))
         for k in keys:
-            assert rel_err(_np(g[k]).reshape(go[k].shape), _np(gr[k]).reshape(go[k].shape)) < GRAD_TOL, ("ref", k)
+            assert rel_err(_np(g[k]).reshape(go[k].shape), _np(gr[k]).reshape(go[k].shape), fl[k]) < GRAD_TOL, ("ref", k)
             # the reference itself (float atomics) is held to the same bar against the fp64-accumulating oracle
-            assert rel_err(_np(gr[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, ("ref-vs-oracle", k)
+            assert rel_err(_np(gr[k]).reshape(go[k].shape), go[k], fl[k]) < GRAD_TOL, ("ref-vs-oracle", k)
     # rows of culled Gaussians are written as zeros (outputs are not pre-zeroed by the caller)
     culled = ~(fw["radii"] > 0)
     for k in keys:
