@@ -229,6 +229,20 @@ int e3_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 	return 0;
 }
 
+size_t e3_scan_scratch_bytes(size_t n) { return (e3_scan_blocks(n) + 2) * sizeof(uint32_t); }
+
+int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch, size_t scratch_bytes,
+	uint32_t* total, void* stream)
+{
+	if (n == 0) {
+		if (total) E3_CHECK(cudaMemsetAsync(total, 0, sizeof(uint32_t), (cudaStream_t)stream));
+		return 0;
+	}
+	if (!in || !out || !scratch || scratch_bytes < e3_scan_scratch_bytes(n)) return E3_ERR_BAD_ARGUMENT;
+	E3_CHECK(e3_exclusive_scan_u32(in, nullptr, out, n, static_cast<uint32_t*>(scratch), total, (cudaStream_t)stream));
+	return 0;
+}
+
 unsigned long long e3_kernel_launches(void) { return g_e3_launches; }
 
 int e3_profile_enable(unsigned stage_mask)

@@ -252,8 +252,18 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 		key = __float_as_uint(pview_z);
 		depths[idx] = pview_z;
 		rec[3 * idx] = make_float4(pix, piy, conic.x, conic.y);
-		rec[3 * idx + 1] = make_float4(conic.z, __ldg(opacities + idx), col[0], col[1]);
-		rec[3 * idx + 2] = make_float4(col[2], 0.f, 0.f, 0.f);
+		// half-extent of the bounding box of { alpha >= 1/255 } = { power >= -ln(255 opacity) }:
+		// sqrt(2 tau cov_xx), sqrt(2 tau cov_yy) (cov = inverse of the conic). Margins make the
+		// box a strict superset under fp32 rounding of the blend's own power evaluation.
+		const float opac = __ldg(opacities + idx);
+		const float tau = __logf(255.0f * opac) + 1e-3f;
+		float ext_x = -1.f, ext_y = -1.f;
+		if (tau > 0.f) {
+			ext_x = sqrtf(2.0f * tau * cov.x) * 1.0005f + 0.02f;
+			ext_y = sqrtf(2.0f * tau * cov.z) * 1.0005f + 0.02f;
+		}
+		rec[3 * idx + 1] = make_float4(conic.z, opac, col[0], col[1]);
+		rec[3 * idx + 2] = make_float4(col[2], ext_x, ext_y, 0.f);
 	} while (0);
 	radii[idx] = my_radius;
 	tiles_touched[idx] = tt;

@@ -31,6 +31,23 @@ __device__ __forceinline__ void pixel_of_thread(int& lx, int& ly)
 	ly = ((w >> 1) << 2) + (lane >> 3);
 }
 
+// Which of the tile's eight 8x4 warp blocks can an instance touch at all? A pixel receives a
+// contribution only if alpha = opacity * exp(power) >= 1/255, i.e. inside the ellipse
+// power >= -ln(255 * opacity); (hx, hy) is the half-extent of that ellipse's bounding box,
+// precomputed per Gaussian with a safety margin (preprocess.cu). Bit w = (row r)*2 + (column c)
+// matches pixel_of_thread(). The test is conservative, so skipping changes no result bit.
+__device__ __forceinline__ uint32_t subtile_mask(float x, float y, float hx, float hy)
+{
+	if (!(hx >= 0.f)) return 0u;
+	const float xl = x - hx, xh = x + hx, yl = y - hy, yh = y + hy;
+	const uint32_t cm = ((xh >= 0.f) & (xl <= 7.f)) | (((xh >= 8.f) & (xl <= 15.f)) << 1);
+	uint32_t m = 0;
+#pragma unroll
+	for (int r = 0; r < 4; r++)
+		if ((yh >= 4.f * r) & (yl <= 4.f * r + 3.f)) m |= cm << (2 * r);
+	return m;
+}
+
 // forward.cu:335 with the reference's contraction
 __device__ __forceinline__ float eval_power(float dx, float dy, float cx, float cy, float cz)
 {
@@ -47,12 +64,15 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 	__shared__ float4 sA[kBatch];   // x, y, conic.x, conic.y
 	__shared__ float4 sB[kBatch];   // conic.z, opacity, c0, c1
 	__shared__ float sC[kBatch];    // c2
+	__shared__ uint8_t sMask[kBatch];
 	int lx, ly;
 	pixel_of_thread(lx, ly);
+	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 	const int px = blockIdx.x * E3_TILE_X + lx, py = blockIdx.y * E3_TILE_Y + ly;
 	const bool inside = px < W && py < H;
 	const uint32_t pix_id = (uint32_t)W * py + px;
 	const float pixfx = (float)px, pixfy = (float)py;
+	const float tile_x0 = (float)(blockIdx.x * E3_TILE_X), tile_y0 = (float)(blockIdx.y * E3_TILE_Y);
 	const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
 	const int total = (int)(range.y - range.x);
 	bool done = !inside;
@@ -68,30 +88,41 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 		if (k < total) {
 			const uint32_t id = point_list[range.x + k];
 			const float4* r = rec + 3 * (size_t)id;
-			sA[threadIdx.x] = __ldg(r);
+			const float4 a = __ldg(r);
+			const float4 e = __ldg(r + 2);     // c2, hx, hy, -
+			sA[threadIdx.x] = a;
 			sB[threadIdx.x] = __ldg(r + 1);
-			if (C == 3) sC[threadIdx.x] = __ldg(reinterpret_cast<const float*>(r + 2));
+			if (C == 3) sC[threadIdx.x] = e.x;
+			sMask[threadIdx.x] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
 		}
 		__syncthreads();
 		if (__all_sync(E3_FULL, done)) continue;    // this warp's 32 pixels are finished
 		const int nb = min(kBatch, total - b0);
-		for (int j = 0; !done && j < nb; j++) {
-			const float4 a = sA[j];
-			const float4 b = sB[j];
-			const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
-			const float power = eval_power(dx, dy, a.z, a.w, b.x);
-			if (power > 0.0f) continue;
-			const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
-			if (alpha < 1.0f / 255.0f) continue;
-			const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
-			if (test_T < 0.0001f) { done = true; continue; }
-			Cacc[0] = __fmaf_rn(T, __fmul_rn(alpha, b.z), Cacc[0]);
-			if (C == 3) {
-				Cacc[1] = __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]);
-				Cacc[2] = __fmaf_rn(T, __fmul_rn(alpha, sC[j]), Cacc[2]);
+		for (int c0 = 0; c0 < nb; c0 += 32) {
+			const int jj = c0 + lane;
+			uint32_t m = __ballot_sync(E3_FULL, jj < nb && ((sMask[jj] >> w) & 1u));
+			while (m) {
+				const int j = c0 + __ffs(m) - 1;
+				m &= m - 1;
+				if (done) continue;
+				const float4 a = sA[j];
+				const float4 b = sB[j];
+				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
+				const float power = eval_power(dx, dy, a.z, a.w, b.x);
+				if (power > 0.0f) continue;
+				const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+				if (alpha < 1.0f / 255.0f) continue;
+				const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
+				if (test_T < 0.0001f) { done = true; continue; }
+				Cacc[0] = __fmaf_rn(T, __fmul_rn(alpha, b.z), Cacc[0]);
+				if (C == 3) {
+					Cacc[1] = __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]);
+					Cacc[2] = __fmaf_rn(T, __fmul_rn(alpha, sC[j]), Cacc[2]);
+				}
+				T = test_T;
+				last_contributor = (uint32_t)(b0 + j + 1);
 			}
-			T = test_T;
-			last_contributor = (uint32_t)(b0 + j + 1);
+			if (__all_sync(E3_FULL, done)) break;
 		}
 	}
 	if (inside) {
@@ -146,6 +177,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	__shared__ float4 sB[kBatch];
 	__shared__ float sC[kBatch];
 	__shared__ uint32_t sId[kBatch];
+	__shared__ uint8_t sMask[kBatch];
 	__shared__ int s_max[8];
 	int lx, ly;
 	pixel_of_thread(lx, ly);
@@ -154,6 +186,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	const bool inside = px < W && py < H;
 	const uint32_t pix_id = (uint32_t)W * py + px;
 	const float pixfx = (float)px, pixfy = (float)py;
+	const float tile_x0 = (float)(blockIdx.x * E3_TILE_X), tile_y0 = (float)(blockIdx.y * E3_TILE_Y);
 	const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
 	const float T_final = inside ? final_Ts[pix_id] : 0.f;
 	float T = T_final;
@@ -190,16 +223,24 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 		if (k < total) {
 			const uint32_t id = point_list[range.x + (total - 1 - k)];
 			const float4* r = rec + 3 * (size_t)id;
+			const float4 a = __ldg(r);
+			const float4 e = __ldg(r + 2);
 			sId[threadIdx.x] = id;
-			sA[threadIdx.x] = __ldg(r);
+			sA[threadIdx.x] = a;
 			sB[threadIdx.x] = __ldg(r + 1);
-			if (C == 3) sC[threadIdx.x] = __ldg(reinterpret_cast<const float*>(r + 2));
+			if (C == 3) sC[threadIdx.x] = e.x;
+			sMask[threadIdx.x] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
 		}
 		__syncthreads();
 		const int nb = min(kBatch, total - b0);
 		// skip the part of the batch that lies behind this warp's deepest contributor
-		int j0 = max(0, (total - b0) - wmax);
-		for (int j = j0; j < nb; j++) {
+		const int j0 = max(0, (total - b0) - wmax);
+		for (int c0 = (j0 & ~31); c0 < nb; c0 += 32) {
+		const int jj = c0 + lane;
+		uint32_t m = __ballot_sync(E3_FULL, jj < nb && jj >= j0 && ((sMask[jj] >> w) & 1u));
+		while (m) {
+			const int j = c0 + __ffs(m) - 1;
+			m &= m - 1;
 			const int contributor = total - 1 - (b0 + j);
 			const float4 a = sA[j];
 			const float4 b = sB[j];
@@ -253,6 +294,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 				if (C == 3 || slot < 7) atomicAdd(dst + slot, v[0]);
 			}
 			if (C == 3 && lane == 1) atomicAdd(dst + 8, v8);
+		}
 		}
 	}
 }

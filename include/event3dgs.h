@@ -130,6 +130,16 @@ E3_API int e3_rasterize_backward(
 E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,
 	const float* projmatrix, uint8_t* present, void* stream);
 
+/* Exclusive prefix sum of n uint32 values: out[i] = in[0] + ... + in[i-1]; *total (optional,
+ * device) receives the sum of all n. Replaces the cub::DeviceScan::InclusiveSum over
+ * tiles_touched and its temp-storage size query (cuda_rasterizer/rasterizer_impl.cu:166,277):
+ * the forward uses this kernel for the instance offsets; the reference's inclusive value is
+ * out[i] + in[i] and its num_rendered is *total. `scratch` is caller-owned device memory of at
+ * least e3_scan_scratch_bytes(n) bytes, 4-byte aligned, contents irrelevant. in == out is allowed. */
+E3_API size_t e3_scan_scratch_bytes(size_t n);
+E3_API int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch,
+	size_t scratch_bytes, uint32_t* total, void* stream);
+
 /* Optional per-stage device timing, used by bench.py for the roofline of the dominant kernel.
  * No counterpart in the reference (it only brackets the whole iteration with two CUDA events,
  * train.py:64-65,95,299). While bit `s` of stage_mask is set, every launch group of stage `s` is

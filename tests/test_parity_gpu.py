@@ -265,3 +265,26 @@ def test_full_size_c3_properties(gc):
     assert rel_err(_np(fw1["color"]), np.ones((3, 720, 1280), np.float32)) < IMG_TOL   # alpha + T = 1
     g = gc.ours_backward(fw, inp, smooth_dL(3, 720, 1280))
     assert all(bool(torch.isfinite(v).all()) for v in g.values())
+
+
+def test_exclusive_scan_entry_point(gc):
+    """e3_exclusive_scan (the instance-offset scan) against numpy, ragged and maximum-ish sizes."""
+    from event_3dgs_b200 import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(0)
+    for n in (1, 2, 255, 2048, 2049, 100_003, 3_000_000, 16_777_216 + 5):
+        a = rng.integers(0, 40, n, dtype=np.uint32)
+        src = gc.T(a.view(np.int32))
+        out = torch.empty_like(src)
+        tot = torch.zeros(1, dtype=torch.int32, device=src.device)
+        nb = L.e3_scan_scratch_bytes(n)
+        scratch = torch.empty(nb, dtype=torch.uint8, device=src.device)
+        _lib.check(L.e3_exclusive_scan(src.data_ptr(), out.data_ptr(), n, scratch.data_ptr(), nb, tot.data_ptr(),
+                                       torch.cuda.current_stream().cuda_stream))
+        ref = np.cumsum(a.astype(np.uint64))
+        assert int(tot.item()) == int(ref[-1])
+        got = _np(out).view(np.uint32)
+        assert got[0] == 0 and (got[1:] == ref[:-1].astype(np.uint32)).all()
+    # too little scratch is rejected before any launch
+    assert L.e3_exclusive_scan(src.data_ptr(), out.data_ptr(), n, scratch.data_ptr(), 4, None, None) == -1
+    assert L.e3_exclusive_scan(None, None, 0, None, 0, None, None) == 0
