@@ -30,6 +30,8 @@ SIGNATURES = {
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "e3_scan_scratch_bytes": (_sz, [_sz]),
     "e3_exclusive_scan": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _vp]),
+    "e3_exclusive_scan_noalloc_max": (_sz, []),
+    "e3_exclusive_scan_noalloc": (_i, [_vp, _vp, _sz, _vp, _vp]),
     "e3_profile_enable": (_i, [ctypes.c_uint]),
     "e3_kernel_launches": (ctypes.c_ulonglong, []),
     "e3_profile_read": (_i, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), _i]),

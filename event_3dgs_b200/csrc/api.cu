@@ -86,6 +86,7 @@ const char* e3_error_string(int code)
 	case E3_ERR_ALLOC_FAILED: return "event3dgs: workspace allocation callback returned NULL";
 	case E3_ERR_PREFILTERED: return "Point is filtered although prefiltered is set. This shouldn't happen!";
 	case E3_ERR_UNSUPPORTED: return "For non-RGB, provide precomputed Gaussian colors!";
+	case E3_ERR_TOO_LARGE: return "event3dgs: input larger than this entry point's fixed capacity (e3_exclusive_scan_noalloc: at most 16777216 values)";
 	}
 	if (code > 0) return cudaGetErrorString((cudaError_t)code);
 	return "event3dgs: unknown error";

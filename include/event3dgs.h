@@ -140,6 +140,23 @@ E3_API size_t e3_scan_scratch_bytes(size_t n);
 E3_API int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch,
 	size_t scratch_bytes, uint32_t* total, void* stream);
 
+/* The same prefix sum for callers that cannot supply scratch memory. No counterpart in the
+ * reference. Meant for hosts that may not allocate when they call us: a render or serving loop
+ * that reserved all device memory up front and bans cudaMalloc in the loop (it synchronises the
+ * device), or a plugin host that passes inputs and outputs only. The block sums live in a
+ * 32.8 KB array inside the library (present on every GPU that loads it, until exit); the call
+ * allocates nothing. n may not exceed E3_NOALLOC_SCAN_MAX, else E3_ERR_TOO_LARGE is returned and
+ * nothing runs. The first call on a device resolves the array's device address (do it at
+ * start-up, before any stream capture). All calls on a device share the array: calls that
+ * overlap on the GPU race with each other, so keep them on one stream or order them with
+ * events. Nothing in the array needs to be zero beforehand (every word is written before it is
+ * read), so left-over contents of an earlier call are harmless. in == out is allowed. */
+#define E3_NOALLOC_SCAN_MAX 16777216
+#define E3_ERR_TOO_LARGE (-5)      /* input exceeds a fixed-capacity entry point's maximum */
+E3_API size_t e3_exclusive_scan_noalloc_max(void);
+E3_API int e3_exclusive_scan_noalloc(const uint32_t* in, uint32_t* out, size_t n,
+	uint32_t* total, void* stream);
+
 /* Optional per-stage device timing, used by bench.py for the roofline of the dominant kernel.
  * No counterpart in the reference (it only brackets the whole iteration with two CUDA events,
  * train.py:64-65,95,299). While bit `s` of stage_mask is set, every launch group of stage `s` is
