@@ -27,6 +27,11 @@ SIGNATURES = {
     "e3_rasterize_backward": (_i, [_i, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp,
                                    _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "e3_rasterize_forward_raw": (_i, [ALLOC_FN, _vp, ALLOC_FN, _vp, ALLOC_FN, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp,
+                                      _vp, _f, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp, ctypes.POINTER(_i)]),
+    "e3_rasterize_backward_raw": (_i, [_i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
+                                       _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "e3_scan_scratch_bytes": (_sz, [_sz]),
     "e3_exclusive_scan": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _vp]),

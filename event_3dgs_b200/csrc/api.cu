@@ -114,13 +114,14 @@ size_t e3_binning_bytes(int num_rendered)
 	return (size_t)end + 256;
 }
 
-int e3_rasterize_forward(
+static int forward_impl(
 	e3_alloc_fn geometry_alloc, void* geometry_ctx,
 	e3_alloc_fn binning_alloc, void* binning_ctx,
 	e3_alloc_fn image_alloc, void* image_ctx,
 	int P, int D, int M, int channels,
 	const float* background, int width, int height,
-	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* means3D, const float* shs, const float* f_rest, bool raw, const float* colors_precomp,
+	const float* opacities,
 	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
 	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
 	float tan_fovx, float tan_fovy, int prefiltered,
@@ -148,7 +149,7 @@ int e3_rasterize_forward(
 	E3ImageState im = E3ImageState::carve(ibuf, N, T);
 
 	E3_CHECK(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), st));
-	E3_STAGE(E3_STAGE_PREPROCESS_FWD, e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+	E3_STAGE(E3_STAGE_PREPROCESS_FWD, e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, f_rest, raw, cov3D_precomp, colors_precomp,
 		viewmatrix, projmatrix, cam_pos, prefiltered != 0, radii, g, st));
 
 	// depth order of the Gaussians (culled ones carry key 0xffffffff and emit nothing)
@@ -182,6 +183,44 @@ int e3_rasterize_forward(
 	return 0;
 }
 
+int e3_rasterize_forward(
+	e3_alloc_fn geometry_alloc, void* geometry_ctx,
+	e3_alloc_fn binning_alloc, void* binning_ctx,
+	e3_alloc_fn image_alloc, void* image_ctx,
+	int P, int D, int M, int channels,
+	const float* background, int width, int height,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy, int prefiltered,
+	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host)
+{
+	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, channels,
+		background, width, height, means3D, shs, nullptr, false, colors_precomp, opacities, scales, scale_modifier, rotations,
+		cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, radii, debug, stream,
+		num_rendered_host);
+}
+
+int e3_rasterize_forward_raw(
+	e3_alloc_fn geometry_alloc, void* geometry_ctx,
+	e3_alloc_fn binning_alloc, void* binning_ctx,
+	e3_alloc_fn image_alloc, void* image_ctx,
+	int P, int active_sh_degree,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy,
+	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host)
+{
+	if (active_sh_degree < 0 || active_sh_degree > 3) return E3_ERR_BAD_ARGUMENT;
+	if (P > 0 && (!features_dc || (active_sh_degree > 0 && !features_rest))) return E3_ERR_BAD_ARGUMENT;
+	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, active_sh_degree, 16, 3,
+		background, width, height, xyz, features_dc, features_rest, true, nullptr, opacity_logits, log_scales, scale_modifier,
+		raw_rotations, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, 0, out_color, radii, debug, stream,
+		num_rendered_host);
+}
+
 int e3_rasterize_backward(
 	int P, int D, int M, int R, int channels,
 	const float* background, int width, int height,
@@ -213,9 +252,61 @@ int e3_rasterize_backward(
 		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
-	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, means3D, radii, shs, scales, rotations, cov3D_precomp, viewmatrix,
-		projmatrix, campos, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh,
-		dL_dscale, dL_drot, st));
+	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, means3D, radii, shs, nullptr, nullptr, false, false, scales, rotations,
+		cov3D_precomp, viewmatrix, projmatrix, campos, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh,
+		nullptr, dL_dscale, dL_drot, st));
+	return 0;
+}
+
+int e3_rasterize_backward_raw(
+	int P, int active_sh_degree, int R,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, int accumulate,
+	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
+	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
+	int debug, void* stream)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	if (P < 0 || active_sh_degree < 0 || active_sh_degree > 3) return E3_ERR_BAD_ARGUMENT;
+	if (P == 0) return 0;
+	if (!geometry_buffer || !image_buffer || (R > 0 && !binning_buffer) || !radii || !xyz || !features_dc || !opacity_logits ||
+		!log_scales || !raw_rotations || !dL_dpix || !d_xyz || !d_features_dc || !d_opacity_logits || !d_log_scales ||
+		!d_raw_rotations || !viewmatrix || !projmatrix || !campos)
+		return E3_ERR_BAD_ARGUMENT;
+	if (active_sh_degree > 0 && (!features_rest || !d_features_rest)) return E3_ERR_BAD_ARGUMENT;
+	E3Frame f = make_frame(P, active_sh_degree, 16, 3, width, height, tan_fovx, tan_fovy, scale_modifier);
+	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
+	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
+	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
+	if (R > 0) {
+		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
+		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+			dL_dpix, g.acc, st));
+	}
+	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,
+		accumulate != 0, log_scales, raw_rotations, nullptr, viewmatrix, projmatrix, campos, g, d_mean2D, nullptr, d_opacity_logits,
+		nullptr, d_xyz, nullptr, d_features_dc, active_sh_degree > 0 ? d_features_rest : nullptr, d_log_scales, d_raw_rotations, st));
+	return 0;
+}
+
+int e3_event_loss(int width, int height, const float* image, const float* image_now, const float* image_next,
+	const float* gt_now, const float* gt_next, const float* gt_intensity, const float* gt_blur, const float* c,
+	float upstream, void* scratch, size_t scratch_bytes, float* d_image, float* d_image_now, float* d_image_next,
+	float* out5, void* stream)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	const int debug = 0;
+	if (width <= 0 || height <= 0 || !image || !image_now || !image_next || !gt_now || !gt_next || !gt_intensity || !c ||
+		!scratch || scratch_bytes < 8 * sizeof(double) || (reinterpret_cast<size_t>(scratch) & 7) || !d_image || !d_image_now ||
+		!d_image_next || !out5)
+		return E3_ERR_BAD_ARGUMENT;
+	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_loss((size_t)width * height, image, image_now, image_next, gt_now, gt_next,
+		gt_intensity, gt_blur, c, upstream, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
 	return 0;
 }
 

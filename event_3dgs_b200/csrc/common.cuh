@@ -122,17 +122,21 @@ struct E3Frame {
 };
 
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
-	const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
-	const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
+	const float* rotations, const float* opacities, const float* shs, const float* f_rest, bool raw,
+	const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
 	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st);
 cudaError_t e3_launch_mark_visible(int P, const float* means3D, const float* viewmatrix,
 	uint8_t* present, cudaStream_t st);
 cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D,
-	const int* radii, const float* shs, const float* scales, const float* rotations,
+	const int* radii, const float* shs, const float* f_rest, const float* opacities_raw, bool raw, bool accumulate,
+	const float* scales, const float* rotations,
 	const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
 	const float* campos, const E3GeomState& g, float* dL_dmean2D, float* dL_dconic,
-	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* d_frest,
 	float* dL_dscale, float* dL_drot, cudaStream_t st);
+cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
+	const float* gt_now, const float* gt_next, const float* gt_int, const float* gt_blur, const float* c_ptr,
+	float upstream, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st);
 
 // out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (optional, device) = sum of all
 cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint32_t* out,

@@ -112,15 +112,17 @@ __constant__ float kSH_C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.45
 #define SH_C1 0.4886025119029199f
 
 // forward.cu:20-71
-__device__ __forceinline__ float3 sh_to_color(int deg, const float* __restrict__ sh, float dx, float dy,
-	float dz, uint8_t* clamped)
+// sh0 = the degree-0 coefficient [3], shr = coefficients 1.. [(M-1),3] (contiguous after sh0 in
+// the reference's [P,M,3] layout; a separate tensor, features_rest, in the raw-parameter path)
+__device__ __forceinline__ float3 sh_to_color(int deg, const float* __restrict__ sh0, const float* __restrict__ shr,
+	float dx, float dy, float dz, uint8_t* clamped)
 {
 	const float len = sqrtf(dx * dx + dy * dy + dz * dz);
 	const float x = dx / len, y = dy / len, z = dz / len;
 	float res[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
-#define S(k) sh[3 * (k) + c]
+#define S(k) ((k) == 0 ? sh0[c] : shr[3 * ((k) - 1) + c])
 		float v = SH_C0 * S(0);
 		if (deg > 0) {
 			v = v - SH_C1 * y * S(1) + SH_C1 * z * S(2) - SH_C1 * x * S(3);
@@ -162,12 +164,16 @@ __device__ __forceinline__ void stage_rows(const float* __restrict__ src, size_t
 	}
 }
 
-template <int C>
+// RAW = the inputs are the leaf parameters of scene/gaussian_model.py (log-scales, unnormalised
+// quaternions, opacity logits, features_dc / features_rest): the activations of
+// gaussian_model.py:95-115 and the SH -> colour of gaussian_renderer/__init__.py:77-81 are
+// evaluated here instead of by ~60 PyTorch launches per render (K15 of SURVEY.md section 2b).
+template <int C, bool RAW>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 	int P, int D, int M,
 	const float* __restrict__ means3D, const float* __restrict__ scales, float mod,
 	const float* __restrict__ rotations, const float* __restrict__ opacities,
-	const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+	const float* __restrict__ shs, const float* __restrict__ f_rest, const float* __restrict__ cov3D_precomp,
 	const float* __restrict__ colors_precomp, const float* __restrict__ vm_g,
 	const float* __restrict__ pm_g, const float* __restrict__ campos,
 	int W, int H, float tan_fovx, float tan_fovy, float focal_x, float focal_y, int gx, int gy,
@@ -193,6 +199,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 	const size_t idx = first + t;
 	const float* vm = s_m;
 	const float* pm = s_m + 16;
+	if (RAW) {    // scaling_activation = exp (gaussian_model.py:28)
+		s_scl[3 * t] = expf(s_scl[3 * t]); s_scl[3 * t + 1] = expf(s_scl[3 * t + 1]); s_scl[3 * t + 2] = expf(s_scl[3 * t + 2]);
+	}
 
 	// zero this Gaussian's backward accumulator while we are streaming over it anyway
 	float4* a4 = reinterpret_cast<float4*>(acc + idx * E3_ACC_STRIDE);
@@ -217,7 +226,11 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 #pragma unroll
 			for (int i = 0; i < 6; i++) c3[i] = cov3D_precomp[idx * 6 + i];
 		} else {
-			const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+			float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+			if (RAW) {    // rotation_activation = F.normalize (gaussian_model.py:36): x / max(|x|, 1e-12)
+				const float inv = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+				q.x *= inv; q.y *= inv; q.z *= inv; q.w *= inv;
+			}
 			cov3d_exact(s_scl[3 * t], s_scl[3 * t + 1], s_scl[3 * t + 2], mod, q.x, q.y, q.z, q.w, c3);
 #pragma unroll
 			for (int i = 0; i < 6; i++) cov3Ds[idx * 6 + i] = c3[i];
@@ -241,7 +254,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 			for (int c = 0; c < C; c++) col[c] = s_col[C * t + c];
 		} else {
 			uint8_t cl[3];
-			const float3 v = sh_to_color(D, shs + idx * M * 3, px - campos[0], py - campos[1], pz - campos[2], cl);
+			const float* sh0 = RAW ? shs + idx * 3 : shs + idx * M * 3;
+			const float* shr = RAW ? f_rest + idx * 45 : sh0 + 3;
+			const float3 v = sh_to_color(D, sh0, shr, px - campos[0], py - campos[1], pz - campos[2], cl);
 			col[0] = v.x; col[1] = v.y; col[2] = v.z;
 			rgb[idx * 3] = v.x; rgb[idx * 3 + 1] = v.y; rgb[idx * 3 + 2] = v.z;
 			clamped[idx * 3] = cl[0]; clamped[idx * 3 + 1] = cl[1]; clamped[idx * 3 + 2] = cl[2];
@@ -255,7 +270,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 		// half-extent of the bounding box of { alpha >= 1/255 } = { power >= -ln(255 opacity) }:
 		// sqrt(2 tau cov_xx), sqrt(2 tau cov_yy) (cov = inverse of the conic). Margins make the
 		// box a strict superset under fp32 rounding of the blend's own power evaluation.
-		const float opac = __ldg(opacities + idx);
+		float opac = __ldg(opacities + idx);
+		if (RAW) opac = 1.0f / (1.0f + expf(-opac));      // opacity_activation = sigmoid
 		const float tau = __logf(255.0f * opac) + 1e-3f;
 		float ext_x = -1.f, ext_y = -1.f;
 		if (tau > 0.f) {
@@ -286,9 +302,12 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 // :278-341). Reads the packed accumulators of the backward blend and writes EVERY output row
 // (zeros for culled Gaussians), so the caller does not pre-zero anything.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void sh_backward(int deg, int M, const float* __restrict__ sh, float dox,
-	float doy, float doz, const uint8_t* __restrict__ cl, const float* dL_dcolor, float* __restrict__ dsh,
-	float3& dmean)
+// dsh0 / dshr: where the gradients of coefficient 0 / coefficients 1.. go. ACC adds to what is
+// there (the raw path sums the three renders of an event iteration into one gradient tensor).
+template <bool ACC>
+__device__ __forceinline__ void sh_backward(int deg, int M, const float* __restrict__ sh0, const float* __restrict__ shr,
+	float dox, float doy, float doz, const uint8_t* __restrict__ cl, const float* dL_dcolor, float* __restrict__ dsh0,
+	float* __restrict__ dshr, float3& dmean)
 {
 	const float len = sqrtf(dox * dox + doy * doy + doz * doz);
 	const float x = dox / len, y = doy / len, z = doz / len;
@@ -296,8 +315,9 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 #pragma unroll
 	for (int c = 0; c < 3; c++) dRGB[c] = cl[c] ? 0.f : dL_dcolor[c];
 	float dRGBdx[3] = { 0, 0, 0 }, dRGBdy[3] = { 0, 0, 0 }, dRGBdz[3] = { 0, 0, 0 };
-#define S(k) sh[3 * (k) + c]
-#define DSH(k, w) { const float ww = (w); _Pragma("unroll") for (int c = 0; c < 3; c++) dsh[3 * (k) + c] = ww * dRGB[c]; }
+#define S(k) ((k) == 0 ? sh0[c] : shr[3 * ((k) - 1) + c])
+#define DSH(k, w) { const float ww = (w); float* dd = (k) == 0 ? dsh0 : dshr + 3 * ((k) - 1); \
+	_Pragma("unroll") for (int c = 0; c < 3; c++) { if (ACC) dd[c] += ww * dRGB[c]; else dd[c] = ww * dRGB[c]; } }
 	DSH(0, SH_C0);
 	int written = 1;
 	if (deg > 0) {
@@ -338,7 +358,8 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 	}
 #undef S
 #undef DSH
-	for (int k = written; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+	if (!ACC && dshr)
+		for (int k = written; k < M; k++) { dshr[3 * (k - 1)] = 0.f; dshr[3 * (k - 1) + 1] = 0.f; dshr[3 * (k - 1) + 2] = 0.f; }
 	const float ddx = dRGBdx[0] * dRGB[0] + dRGBdx[1] * dRGB[1] + dRGBdx[2] * dRGB[2];
 	const float ddy = dRGBdy[0] * dRGB[0] + dRGBdy[1] * dRGB[1] + dRGBdy[2] * dRGB[2];
 	const float ddz = dRGBdz[0] * dRGB[0] + dRGBdz[1] * dRGB[1] + dRGBdz[2] * dRGB[2];
@@ -350,10 +371,22 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 	dmean.z += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
 }
 
-template <int C>
+template <bool ACC>
+__device__ __forceinline__ void put(float* p, float v) { if (ACC) *p += v; else *p = v; }
+
+// RAW: gradients are taken all the way to the leaf parameters (chain rule through exp /
+// normalize / sigmoid and the SH evaluation, i.e. the autograd backward of K15 in SURVEY.md 2b).
+// ACC: add to the output rows instead of overwriting them (renders 2 and 3 of an event iteration
+// accumulate into the gradient tensors written by render 1); rows of culled Gaussians are then
+// left untouched. Pointer roles in RAW mode: shs = features_dc [P,3], f_rest = features_rest
+// [P,15,3], dL_dsh = d features_dc, d_frest = d features_rest (NULL when D == 0: identically 0),
+// dL_dopacity = d opacity logit, dL_dscale = d log-scale, dL_drot = d raw quaternion,
+// dL_dmean2D optional, dL_dcolor / dL_dcov3D / dL_dconic unused (NULL).
+template <int C, bool RAW, bool ACC>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(
 	int P, int D, int M,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
+	const float* __restrict__ f_rest, float* __restrict__ d_frest, const float* __restrict__ opacities_raw,
 	const uint8_t* __restrict__ clamped, const float* __restrict__ scales,
 	const float* __restrict__ rotations, float mod, const float* __restrict__ cov3D_precomp,
 	const float* __restrict__ cov3D_state, const float* __restrict__ vm_g,
@@ -380,13 +413,21 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(
 		// leave the accumulator clean so that a second backward of the same forward is correct
 		a4[0] = a4[1] = a4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
+	if (ACC && !vis) return;
 	// outputs that are plain copies of the accumulators
-	dL_dmean2D[3 * idx] = a0.x; dL_dmean2D[3 * idx + 1] = a0.y; dL_dmean2D[3 * idx + 2] = 0.f;
+	if (dL_dmean2D) { put<ACC>(dL_dmean2D + 3 * idx, a0.x); put<ACC>(dL_dmean2D + 3 * idx + 1, a0.y); if (!ACC) dL_dmean2D[3 * idx + 2] = 0.f; }
 	if (dL_dconic) reinterpret_cast<float4*>(dL_dconic)[idx] = make_float4(a0.z, a0.w, 0.f, a1.x);
-	dL_dopacity[idx] = a1.y;
 	const float dcol[3] = { a1.z, a1.w, a2.x };
+	if (!RAW) {
+		dL_dopacity[idx] = a1.y;
 #pragma unroll
-	for (int c = 0; c < C; c++) dL_dcolor[idx * C + c] = dcol[c];
+		for (int c = 0; c < C; c++) dL_dcolor[idx * C + c] = dcol[c];
+	} else {
+		// sigmoid backward (gaussian_model.py:31): d logit = d opacity * o * (1 - o)
+		float dlogit = 0.f;
+		if (vis) { const float o = 1.0f / (1.0f + expf(-__ldg(opacities_raw + idx))); dlogit = a1.y * o * (1.0f - o); }
+		put<ACC>(dL_dopacity + idx, dlogit);
+	}
 
 	float3 dmean = make_float3(0, 0, 0);
 	float dcov[6] = { 0, 0, 0, 0, 0, 0 };
@@ -464,28 +505,49 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(
 		dmean.x += (proj[0] * m_w - proj[3] * mul1) * gx2 + (proj[1] * m_w - proj[3] * mul2) * gy2;
 		dmean.y += (proj[4] * m_w - proj[7] * mul1) * gx2 + (proj[5] * m_w - proj[7] * mul2) * gy2;
 		dmean.z += (proj[8] * m_w - proj[11] * mul1) * gx2 + (proj[9] * m_w - proj[11] * mul2) * gy2;
-		if (shs)
-			sh_backward(D, M, shs + idx * M * 3, mean.x - campos[0], mean.y - campos[1], mean.z - campos[2],
-				clamped + 3 * idx, dcol, dL_dsh + idx * M * 3, dmean);
-	} else if (shs) {
-		for (int k = 0; k < 3 * M; k++) dL_dsh[idx * M * 3 + k] = 0.f;
+		if (shs) {
+			if (RAW)
+				sh_backward<ACC>(D, 16, shs + idx * 3, f_rest ? f_rest + idx * 45 : nullptr, mean.x - campos[0], mean.y - campos[1],
+					mean.z - campos[2], clamped + 3 * idx, dcol, dL_dsh + idx * 3, d_frest ? d_frest + idx * 45 : nullptr, dmean);
+			else
+				sh_backward<false>(D, M, shs + idx * M * 3, shs + idx * M * 3 + 3, mean.x - campos[0], mean.y - campos[1],
+					mean.z - campos[2], clamped + 3 * idx, dcol, dL_dsh + idx * M * 3, dL_dsh + idx * M * 3 + 3, dmean);
+		}
+	} else if (shs && !ACC) {
+		if (RAW) {
+			dL_dsh[idx * 3] = dL_dsh[idx * 3 + 1] = dL_dsh[idx * 3 + 2] = 0.f;
+			if (d_frest) for (int k = 0; k < 45; k++) d_frest[idx * 45 + k] = 0.f;
+		} else {
+			for (int k = 0; k < 3 * M; k++) dL_dsh[idx * M * 3 + k] = 0.f;
+		}
 	}
-	dL_dmean3D[3 * idx] = dmean.x; dL_dmean3D[3 * idx + 1] = dmean.y; dL_dmean3D[3 * idx + 2] = dmean.z;
+	put<ACC>(dL_dmean3D + 3 * idx, dmean.x); put<ACC>(dL_dmean3D + 3 * idx + 1, dmean.y); put<ACC>(dL_dmean3D + 3 * idx + 2, dmean.z);
+	if (dL_dcov3D) {
 #pragma unroll
-	for (int i = 0; i < 6; i++) dL_dcov3D[6 * idx + i] = dcov[i];
+		for (int i = 0; i < 6; i++) dL_dcov3D[6 * idx + i] = dcov[i];
+	}
 
 	// ---- computeCov3D backward, backward.cu:278-341 ----
 	if (scales) {
 		float ds[3] = { 0, 0, 0 };
 		float4 dq = make_float4(0, 0, 0, 0);
+		float qnorm_inv = 1.f;
+		float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+		float sact[3] = { 1.f, 1.f, 1.f };
 		if (vis) {
-			const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+			q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+			sact[0] = scales[3 * idx]; sact[1] = scales[3 * idx + 1]; sact[2] = scales[3 * idx + 2];
+			if (RAW) {
+				qnorm_inv = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+				q.x *= qnorm_inv; q.y *= qnorm_inv; q.z *= qnorm_inv; q.w *= qnorm_inv;
+				sact[0] = expf(sact[0]); sact[1] = expf(sact[1]); sact[2] = expf(sact[2]);
+			}
 			const float r = q.x, x = q.y, y = q.z, z = q.w;
 			const float R[3][3] = {
 				{ 1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y) },
 				{ 2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x) },
 				{ 2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y) } };
-			const float s[3] = { mod * scales[3 * idx], mod * scales[3 * idx + 1], mod * scales[3 * idx + 2] };
+			const float s[3] = { mod * sact[0], mod * sact[1], mod * sact[2] };
 			float Mx[3][3];
 #pragma unroll
 			for (int c = 0; c < 3; c++)
@@ -510,24 +572,34 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(
 			dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
 			dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
 		}
-		dL_dscale[3 * idx] = ds[0]; dL_dscale[3 * idx + 1] = ds[1]; dL_dscale[3 * idx + 2] = ds[2];
-		reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+		if (RAW) {
+			// exp backward: d log-scale = d scale * scale;  F.normalize backward:
+			// d raw = (d qhat - qhat (qhat . d qhat)) / |raw|
+#pragma unroll
+			for (int i = 0; i < 3; i++) ds[i] *= sact[i];
+			const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+			dq.x = (dq.x - q.x * dot) * qnorm_inv; dq.y = (dq.y - q.y * dot) * qnorm_inv;
+			dq.z = (dq.z - q.z * dot) * qnorm_inv; dq.w = (dq.w - q.w * dot) * qnorm_inv;
+		}
+		put<ACC>(dL_dscale + 3 * idx, ds[0]); put<ACC>(dL_dscale + 3 * idx + 1, ds[1]); put<ACC>(dL_dscale + 3 * idx + 2, ds[2]);
+		put<ACC>(dL_drot + 4 * idx, dq.x); put<ACC>(dL_drot + 4 * idx + 1, dq.y);
+		put<ACC>(dL_drot + 4 * idx + 2, dq.z); put<ACC>(dL_drot + 4 * idx + 3, dq.w);
 	}
 }
 
 }  // namespace
 
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
-	const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
-	const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
+	const float* rotations, const float* opacities, const float* shs, const float* f_rest, bool raw,
+	const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
 	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st)
 {
 	const int grid = (f.P + 255) / 256;
-#define LAUNCH(CH) preprocess_fwd_kernel<CH><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
-	rotations, opacities, shs, cov3D_precomp, colors_precomp, viewmatrix, projmatrix, cam_pos, f.W, f.H, \
+#define LAUNCH(CH, RW) preprocess_fwd_kernel<CH, RW><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
+	rotations, opacities, shs, f_rest, cov3D_precomp, colors_precomp, viewmatrix, projmatrix, cam_pos, f.W, f.H, \
 	f.tan_fovx, f.tan_fovy, f.focal_x, f.focal_y, f.gx, f.gy, prefiltered, radii, g.depths, g.rec, g.cov3D, g.rgb, \
 	g.clamped, g.tiles_touched, g.rect, g.dkey[0], g.dval[0], g.acc, g.flags)
-	if (f.C == 1) LAUNCH(1); else LAUNCH(3);
+	if (raw) LAUNCH(3, true); else if (f.C == 1) LAUNCH(1, false); else LAUNCH(3, false);
 #undef LAUNCH
 	g_e3_launches += 1;
 	return cudaGetLastError();
@@ -542,18 +614,20 @@ cudaError_t e3_launch_mark_visible(int P, const float* means3D, const float* vie
 }
 
 cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D,
-	const int* radii, const float* shs, const float* scales, const float* rotations,
+	const int* radii, const float* shs, const float* f_rest, const float* opacities_raw, bool raw, bool accumulate,
+	const float* scales, const float* rotations,
 	const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
 	const float* campos, const E3GeomState& g, float* dL_dmean2D, float* dL_dconic,
-	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* d_frest,
 	float* dL_dscale, float* dL_drot, cudaStream_t st)
 {
 	const int grid = (f.P + 255) / 256;
-#define LAUNCH(CH) preprocess_bwd_kernel<CH><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, radii, shs, g.clamped, scales, \
-	rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, f.focal_y, \
-	f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
+#define LAUNCH(CH, RW, AC) preprocess_bwd_kernel<CH, RW, AC><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
+	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
+	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
 	dL_dscale, dL_drot)
-	if (f.C == 1) LAUNCH(1); else LAUNCH(3);
+	if (raw) { if (accumulate) LAUNCH(3, true, true); else LAUNCH(3, true, false); }
+	else if (f.C == 1) LAUNCH(1, false, false); else LAUNCH(3, false, false);
 #undef LAUNCH
 	g_e3_launches += 1;
 	return cudaGetLastError();

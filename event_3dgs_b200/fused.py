@@ -1,0 +1,151 @@
+"""Fused event iteration: the reference's train.py:144-212 hot section (3 renders + event loss +
+loss.backward()) with the PyTorch glue folded into the CUDA kernels.
+
+  * activations + SH -> colour inside the preprocess kernels (e3_rasterize_forward_raw /
+    e3_rasterize_backward_raw) instead of ~60 ATen launches per render and their autograd backward;
+  * the event loss and its three backward seeds in two streaming kernels (e3_event_loss) instead
+    of ~50 launches; the dead ssim_gray evaluation (lambda_dssim = 0, train.py:177-178) is gone;
+  * the three backward passes add into ONE set of gradient tensors (no autograd graph at all).
+
+The result is what `loss.backward()` leaves in the reference: .grad on the six leaf tensors and on
+the event threshold c, plus the first render's screen-space gradient for the densification
+statistics (train.py:317-320). The drop-in path (pipeline.py) stays the reference-shaped one.
+"""
+import ctypes
+import math
+
+import torch
+
+from . import _lib
+from .rasterizer import _ALLOC_CB, _slots
+
+
+class RenderState:
+    __slots__ = ("R", "color", "radii", "geom", "binning", "img", "cam", "tanfovx", "tanfovy")
+
+
+def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False):
+    L = _lib.lib()
+    xyz = pc._xyz
+    P = xyz.shape[0]
+    dev = xyz.device
+    H, W = int(cam.image_height), int(cam.image_width)
+    st = RenderState()
+    st.cam = cam
+    st.tanfovx = math.tan(cam.FoVx * 0.5)
+    st.tanfovy = math.tan(cam.FoVy * 0.5)
+    st.radii = torch.empty(P, dtype=torch.int32, device=dev)
+    empty = torch.empty(0, dtype=torch.uint8, device=dev)
+    if P == 0:
+        st.R, st.color, st.geom, st.binning, st.img = 0, torch.zeros(3, H, W, device=dev), empty, empty, empty
+        return st
+    st.color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+    D = int(pc.active_sh_degree)
+    R = ctypes.c_int(0)
+    _slots.clear()
+    _slots["device"] = dev
+    with torch.cuda.device(dev):
+        code = L.e3_rasterize_forward_raw(
+            _ALLOC_CB, 1, _ALLOC_CB, 2, _ALLOC_CB, 3, P, D, bg.data_ptr(), W, H, xyz.data_ptr(), pc._features_dc.data_ptr(),
+            pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(), float(scaling_modifier),
+            pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(), cam.full_proj_transform.data_ptr(),
+            cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.color.data_ptr(), st.radii.data_ptr(), int(debug),
+            torch.cuda.current_stream(dev).cuda_stream, ctypes.byref(R))
+    st.geom, st.binning, st.img = _slots.get(1, empty), _slots.get(2, empty), _slots.get(3, empty)
+    _slots.clear()
+    _lib.check(code)
+    st.R = R.value
+    return st
+
+
+def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling_modifier=1.0, debug=False):
+    L = _lib.lib()
+    xyz = pc._xyz
+    P = xyz.shape[0]
+    if P == 0:
+        return
+    dev = xyz.device
+    cam = st.cam
+    D = int(pc.active_sh_degree)
+    with torch.cuda.device(dev):
+        code = L.e3_rasterize_backward_raw(
+            P, D, st.R, bg.data_ptr(), int(cam.image_width), int(cam.image_height), xyz.data_ptr(),
+            pc._features_dc.data_ptr(), pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(),
+            float(scaling_modifier), pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(),
+            cam.full_proj_transform.data_ptr(), cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.radii.data_ptr(),
+            st.geom.data_ptr(), st.binning.data_ptr() if st.R > 0 else None, st.img.data_ptr(), dL_dpix.data_ptr(),
+            int(bool(accumulate)), grads["xyz"].data_ptr(), grads["features_dc"].data_ptr(),
+            grads["features_rest"].data_ptr() if D > 0 else None, grads["opacity"].data_ptr(), grads["scaling"].data_ptr(),
+            grads["rotation"].data_ptr(), None if d_mean2D is None else d_mean2D.data_ptr(), int(debug),
+            torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(code)
+
+
+def event_loss_and_seeds(image, image_now, image_next, gt, c, deblur=False, upstream=1.0):
+    """e3_event_loss: returns (out5 tensor [loss, dL/dc, loss1, loss2, f], seeds dict)."""
+    L = _lib.lib()
+    dev = image.device
+    _, H, W = image.shape
+    seeds = {k: torch.empty_like(image) for k in ("image", "image_now", "image_next")}
+    out = torch.empty(5, dtype=torch.float32, device=dev)
+    scratch = torch.empty(8, dtype=torch.float64, device=dev)
+    blur = gt["blurry"] if deblur else None
+    with torch.cuda.device(dev):
+        code = L.e3_event_loss(W, H, image.data_ptr(), image_now.data_ptr(), image_next.data_ptr(),
+                               gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr(),
+                               None if blur is None else blur.data_ptr(), c.data_ptr(), float(upstream), scratch.data_ptr(), 64,
+                               seeds["image"].data_ptr(), seeds["image_now"].data_ptr(), seeds["image_next"].data_ptr(),
+                               out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(code)
+    return out, seeds
+
+
+def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False):
+    """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
+    returns the loss (0-dim device tensor). With return_pkg also the first render's package
+    (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes."""
+    for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg,
+              gt["event_now"], gt["event_next"], gt["intensity"]):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise RuntimeError("event_3dgs_b200.fused: tensors must be contiguous float32 CUDA tensors")
+    sts = [_forward_raw(pc, cam, bg) for cam in (cam_train, cam_now, cam_next)]
+    out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
+    D = int(pc.active_sh_degree)
+    grads = {"xyz": torch.empty_like(pc._xyz), "features_dc": torch.empty_like(pc._features_dc),
+             "opacity": torch.empty_like(pc._opacity), "scaling": torch.empty_like(pc._scaling),
+             "rotation": torch.empty_like(pc._rotation),
+             "features_rest": torch.empty_like(pc._features_rest) if D > 0 else _zeros_like_cached(pc._features_rest)}
+    d_mean2D = torch.empty_like(pc._xyz)
+    _backward_raw(pc, sts[0], bg, seeds["image"], grads, False, d_mean2D)
+    _backward_raw(pc, sts[1], bg, seeds["image_now"], grads, True)
+    _backward_raw(pc, sts[2], bg, seeds["image_next"], grads, True)
+    pc._xyz.grad = grads["xyz"]
+    pc._features_dc.grad = grads["features_dc"]
+    pc._features_rest.grad = grads["features_rest"]
+    pc._opacity.grad = grads["opacity"]
+    pc._scaling.grad = grads["scaling"]
+    pc._rotation.grad = grads["rotation"]
+    c.grad = out[1].reshape(c.shape).clone()
+    loss = out[0]
+    if return_pkg:
+        vsp = torch.zeros_like(pc._xyz)
+        vsp.grad = d_mean2D
+        pkg = {"render": sts[0].color, "viewspace_points": vsp, "visibility_filter": sts[0].radii > 0,
+               "radii": sts[0].radii, "num_rendered": [s.R for s in sts], "loss_terms": out}
+        return loss, pkg
+    return loss
+
+
+_ZERO_CACHE = {}
+
+
+def _zeros_like_cached(t):
+    """At SH degree 0 the gradient of features_rest is identically zero; hand out one shared
+    zero tensor instead of filling 180 bytes per Gaussian every iteration. Treat it as read-only."""
+    key = (t.device, tuple(t.shape))
+    z = _ZERO_CACHE.get(key)
+    if z is None:
+        z = torch.zeros_like(t)
+        _ZERO_CACHE.clear()
+        _ZERO_CACHE[key] = z
+    return z

@@ -125,6 +125,60 @@ E3_API int e3_rasterize_backward(
 	int debug,
 	void* stream);
 
+/* Fused variants that take the LEAF parameters of the reference's GaussianModel
+ * (scene/gaussian_model.py:124-147: xyz [P,3], features_dc [P,1,3], features_rest [P,15,3],
+ * scaling = log-scales [P,3], rotation = unnormalised quaternions [P,4], opacity = logits [P,1]).
+ * They replace, in one kernel each way, what render() does in ~60 PyTorch launches per call plus
+ * their autograd backward: the activations exp / F.normalize / sigmoid
+ * (scene/gaussian_model.py:95-115), torch.cat of the SH features (:109-113), the view direction and
+ * eval_sh + clamp_min(x + 0.5, 0) (gaussian_renderer/__init__.py:74-81, utils/sh_utils.py:57-112),
+ * followed by the rasterizer call. active_sh_degree in 0..3; features_rest may be NULL at degree 0.
+ * Always 3 channels. State buffers are interchangeable with e3_rasterize_forward's. */
+E3_API int e3_rasterize_forward_raw(
+	e3_alloc_fn geometry_alloc, void* geometry_ctx,
+	e3_alloc_fn binning_alloc, void* binning_ctx,
+	e3_alloc_fn image_alloc, void* image_ctx,
+	int P, int active_sh_degree,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy,
+	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host);
+
+/* Backward of e3_rasterize_forward_raw down to the leaf parameters (what loss.backward() produces
+ * in the reference through _RasterizeGaussians.backward and the autograd graph of render()).
+ * accumulate = 0: every row of the outputs is written (zeros for culled Gaussians);
+ * accumulate = 1: visible rows are ADDED to the outputs (the three renders of an event iteration
+ * sum into one gradient tensor, like autograd's accumulation into .grad). d_features_rest may be
+ * NULL at degree 0 (it is identically zero). d_mean2D [P,3] is optional: the gradient of the
+ * screen-space means that train.py:319-320 feeds to the densification statistics. */
+E3_API int e3_rasterize_backward_raw(
+	int P, int active_sh_degree, int R,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, int accumulate,
+	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
+	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
+	int debug, void* stream);
+
+/* Event loss of train.py:165-203 (with utils/loss_utils.py:24-28, 234-249, 270-271), value and
+ * backward seeds in two streaming kernels. Inputs are [3,H,W] float images: the three renders
+ * (image = intensity view, image_now / image_next = event views index / index+1), the GT event
+ * frames, the GT intensity frame and, for --deblur, the blurry frame (else NULL). `c` points to the
+ * learnable event threshold on the device (train.py:71,165); the GT threshold is the constant 0.17
+ * (train.py:170). `upstream` scales all gradients (1 for loss.backward()). scratch: >= 64 bytes,
+ * 8-byte aligned device memory. Outputs: the three seeds dL/dimage* [3,H,W] and
+ * out5 = { loss, dL/dc, event L1, intensity L1, fraction of pixels with non-zero GT event }. */
+E3_API int e3_event_loss(int width, int height, const float* image, const float* image_now,
+	const float* image_next, const float* gt_now, const float* gt_next, const float* gt_intensity,
+	const float* gt_blur, const float* c, float upstream, void* scratch, size_t scratch_bytes,
+	float* d_image, float* d_image_now, float* d_image_next, float* out5, void* stream);
+
 /* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
  * rasterizer_impl.cu:54-66,141-153): present[i] = view-space z > 0.2. present is uint8[P]. */
 E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,

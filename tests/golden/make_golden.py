@@ -1,0 +1,78 @@
+"""Generates tests/golden/*.npz by IMPORTING the reference's own python code from /root/reference
+(build container only; the GPU box never runs this). Pins oracle/loss_oracle.py and the host
+mirror event_3dgs_b200/pipeline.py to the reference's utils/loss_utils.py and utils/sh_utils.py.
+
+    python tests/golden/make_golden.py
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REF)
+for name in ("torchgeometry",):                      # imported but unused by utils/loss_utils.py:17
+    sys.modules.setdefault(name, types.ModuleType(name))
+try:
+    import torchvision  # noqa: F401
+except Exception:
+    sys.modules.setdefault("torchvision", types.ModuleType("torchvision"))
+from utils import loss_utils as lu  # noqa: E402
+from utils import sh_utils as su  # noqa: E402
+
+
+def event_case(seed, H, W, deblur, zero_frac):
+    g = torch.Generator().manual_seed(seed)
+    r = lambda: torch.rand(3, H, W, generator=g, dtype=torch.float32) * 0.9 + 0.05
+    image, image_now, image_next = r().requires_grad_(), r().requires_grad_(), r().requires_grad_()
+    q = lambda t: torch.round(t * 255) / 255
+    gt_now = q(r()[:1].repeat(3, 1, 1))
+    gt_next = q(r()[:1].repeat(3, 1, 1))
+    same = torch.rand(1, H, W, generator=g) < zero_frac       # pixels without an event
+    gt_next = torch.where(same, gt_now, gt_next)
+    gt_int, gt_blur = q(r()), q(r())
+    c = torch.tensor(0.17 + 0.05 * seed, requires_grad=True)
+    # ---- train.py:165-203, verbatim flow ----
+    img_diff = lu.differentialable_event_simu(image_now, image_next, False, c)
+    gt_image = lu.differentialable_event_simu(gt_now, gt_next, False, 0.17)
+    Ll1 = lu.l1_loss(img_diff, gt_image)
+    lambda_dssim = 0
+    loss1 = (1.0 - lambda_dssim) * Ll1 + lambda_dssim * (1.0 - lu.ssim_gray(img_diff, gt_image))
+    Ll1b = lu.l1_loss(image, gt_int)
+    loss2 = (1.0 - lambda_dssim) * Ll1b
+    Event_weight = 0.9
+    mask = (gt_image != 0).float()
+    loss = Event_weight * (loss1 * mask).sum() + (1 - Event_weight) * (loss2 * (1 - mask)).sum()
+    loss /= (mask.sum() + (1 - mask).sum())
+    if deblur:
+        blur_alpha = 0.5
+        loss = (1.0 - blur_alpha) * loss + blur_alpha * lu.l1_loss(image, gt_blur)
+    loss.backward()
+    return dict(image=image.detach().numpy(), image_now=image_now.detach().numpy(), image_next=image_next.detach().numpy(),
+                gt_now=gt_now.numpy(), gt_next=gt_next.numpy(), gt_int=gt_int.numpy(), gt_blur=gt_blur.numpy(),
+                c=np.float32(c.item()), deblur=np.bool_(deblur), loss=np.float32(loss.item()),
+                d_image=image.grad.numpy(), d_image_now=image_now.grad.numpy(), d_image_next=image_next.grad.numpy(),
+                d_c=np.float32(c.grad.item()), img_diff=img_diff.detach().numpy(), gt_diff=gt_image.numpy())
+
+
+def sh_case(seed, P):
+    g = torch.Generator().manual_seed(seed)
+    sh = torch.randn(P, 3, 16, generator=g)
+    d = torch.randn(P, 3, generator=g)
+    d = d / d.norm(dim=1, keepdim=True)
+    out = {"sh": sh.numpy(), "dirs": d.numpy()}
+    for deg in range(4):
+        out["rgb%d" % deg] = su.eval_sh(deg, sh, d).numpy()
+    out["rgb2sh"] = su.RGB2SH(torch.linspace(0, 1, 7)).numpy()
+    return out
+
+
+if __name__ == "__main__":
+    np.savez_compressed(os.path.join(HERE, "event_loss_a.npz"), **event_case(0, 24, 40, False, 0.7))
+    np.savez_compressed(os.path.join(HERE, "event_loss_b.npz"), **event_case(1, 17, 33, True, 0.3))
+    np.savez_compressed(os.path.join(HERE, "event_loss_c.npz"), **event_case(2, 16, 16, False, 1.0))   # no events at all
+    np.savez_compressed(os.path.join(HERE, "eval_sh.npz"), **sh_case(3, 64))
+    print("golden vectors written to", HERE)

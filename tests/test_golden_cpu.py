@@ -1,0 +1,77 @@
+"""CPU suite: the python restatements against golden vectors produced by the reference's OWN
+utils/loss_utils.py and utils/sh_utils.py (tests/golden/make_golden.py imports them in the build
+container)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loss_oracle as lo
+from tests.common import rel_err
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(G, "event_loss_*.npz"))))
+def test_loss_oracle_matches_reference_loss_and_autograd(path):
+    d = np.load(path)
+    blur = d["gt_blur"] if bool(d["deblur"]) else None
+    loss, g = lo.event_loss(d["image"], d["image_now"], d["image_next"], d["gt_now"], d["gt_next"], d["gt_int"],
+                            float(d["c"]), blur)
+    assert abs(loss - float(d["loss"])) <= 1e-5 * max(1e-3, abs(float(d["loss"])))
+    assert rel_err(g["image"], d["d_image"]) < 1e-4
+    # the event seeds vanish when the GT has no event at all (case c): compare against a floor
+    fl = 1e-12
+    assert rel_err(g["image_now"], d["d_image_now"], fl) < 1e-4
+    assert rel_err(g["image_next"], d["d_image_next"], fl) < 1e-4
+    assert abs(g["c"] - float(d["d_c"])) <= 1e-4 * max(1e-6, abs(float(d["d_c"])))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(G, "event_loss_*.npz"))))
+def test_pipeline_event_loss_matches_reference(path):
+    from event_3dgs_b200 import pipeline as pl
+    d = np.load(path)
+    t = lambda k: torch.tensor(d[k])
+    image, now, nxt = t("image").requires_grad_(), t("image_now").requires_grad_(), t("image_next").requires_grad_()
+    c = torch.tensor(float(d["c"]), requires_grad=True)
+    loss = pl.event_loss(image, now, nxt, t("gt_now"), t("gt_next"), t("gt_int"), c, t("gt_blur") if bool(d["deblur"]) else None)
+    loss.backward()
+    assert abs(loss.item() - float(d["loss"])) <= 1e-6 * max(1e-3, abs(float(d["loss"])))
+    assert rel_err(image.grad.numpy(), d["d_image"]) < 1e-6
+    assert rel_err(now.grad.numpy(), d["d_image_now"], 1e-12) < 1e-5
+    assert abs(c.grad.item() - float(d["d_c"])) <= 1e-5 * max(1e-6, abs(float(d["d_c"])))
+
+
+def test_pipeline_eval_sh_matches_reference():
+    from event_3dgs_b200 import pipeline as pl
+    d = np.load(os.path.join(G, "eval_sh.npz"))
+    sh, dirs = torch.tensor(d["sh"]), torch.tensor(d["dirs"])
+    for deg in range(4):
+        assert rel_err(pl.eval_sh(deg, sh, dirs).numpy(), d["rgb%d" % deg]) < 1e-6
+    assert rel_err(((np.linspace(0, 1, 7) - 0.5) / pl.C0), d["rgb2sh"]) < 1e-6
+
+
+def test_oracle_sh_colour_matches_reference_eval_sh():
+    """computeColorFromSH of the C oracle (forward.cu:20-71) against the reference's python eval_sh."""
+    from oracle import raster_oracle as ro
+    from tests.common import scene_inputs
+    d = np.load(os.path.join(G, "eval_sh.npz"))
+    P = d["sh"].shape[0]
+    inp = scene_inputs(P, 64, 64, seed=1)
+    campos = inp["campos"]
+    # place the Gaussians along the golden directions in front of the camera
+    means = (campos[None, :] + 3.0 * d["dirs"]).astype(np.float32)
+    shs = np.ascontiguousarray(d["sh"].transpose(0, 2, 1))      # [P,16,3] layout of the rasterizer
+    for deg in range(4):
+        st = ro.rasterize_forward(means, inp["opacities"], inp["viewmatrix"], inp["projmatrix"], campos, inp["bg"], 64, 64,
+                                  inp["tanfovx"], inp["tanfovy"], scales=inp["scales"], rotations=inp["rotations"],
+                                  shs=shs, sh_degree=deg)
+        vis = st["radii"] > 0
+        assert vis.sum() > 3
+        dirs = means - campos[None, :]
+        dirs = dirs / np.linalg.norm(dirs, axis=1, keepdims=True)
+        ref = np.maximum(d["rgb%d" % deg] + 0.5, 0.0)       # gaussian_renderer/__init__.py:81
+        assert np.allclose(dirs, d["dirs"], atol=1e-5)
+        assert rel_err(st["rgb"][vis], ref[vis]) < 1e-4
