@@ -33,6 +33,8 @@ SIGNATURES = {
                                        _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
+    "e3_dist2_scratch_bytes": (_sz, [_i]),
+    "e3_dist2": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "e3_scan_scratch_bytes": (_sz, [_sz]),
     "e3_exclusive_scan": (_i, [_vp, _vp, _sz, _vp, _sz, _vp, _vp]),
     "e3_exclusive_scan_noalloc_max": (_sz, []),

@@ -335,6 +335,22 @@ int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch
 	return 0;
 }
 
+size_t e3_dist2_scratch_bytes(int P)
+{
+	return P > 0 ? e3_knn_scratch_layout(P, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) : 0;
+}
+
+int e3_dist2(int P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes, void* stream)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	const int debug = 0;
+	if (P < 0) return E3_ERR_BAD_ARGUMENT;
+	if (P == 0) return 0;
+	if (!points || !mean_dist2 || !scratch || scratch_bytes < e3_dist2_scratch_bytes(P)) return E3_ERR_BAD_ARGUMENT;
+	E3_STAGE(E3_STAGE_DIST2, e3_launch_dist2(P, points, mean_dist2, static_cast<char*>(scratch), st));
+	return 0;
+}
+
 unsigned long long e3_kernel_launches(void) { return g_e3_launches; }
 
 int e3_profile_enable(unsigned stage_mask)

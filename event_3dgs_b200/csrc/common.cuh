@@ -159,3 +159,9 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges,
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges,
 	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
 	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st);
+
+// knn.cu
+int e3_knn_grid_dim(int P);
+size_t e3_knn_scratch_layout(int P, uint32_t** keys, uint32_t** vals, uint32_t** counts, uint32_t** scan_tmp, uint2** ranges,
+	float4** sorted, uint32_t** bbox, void** grid, char* base);
+cudaError_t e3_launch_dist2(int P, const float* pts, float* out, char* scratch, cudaStream_t st);

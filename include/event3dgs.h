@@ -184,6 +184,16 @@ E3_API int e3_event_loss(int width, int height, const float* image, const float*
 E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,
 	const float* projmatrix, uint8_t* present, void* stream);
 
+/* Replaces simple_knn._C.distCUDA2 (call site scene/gaussian_model.py:134; implementation in the
+ * un-vendored submodule submodules/simple-knn @ 9302c6d): mean_dist2[i] = mean of the squared
+ * Euclidean distances from point i to its 3 nearest OTHER points (exact; coincident points count
+ * with distance 0; fewer than 4 points leave FLT_MAX terms in the mean, as upstream does).
+ * points is float[P,3]; scratch is caller-owned device memory of e3_dist2_scratch_bytes(P) bytes,
+ * 256-byte aligned. */
+E3_API size_t e3_dist2_scratch_bytes(int P);
+E3_API int e3_dist2(int P, const float* points, float* mean_dist2, void* scratch,
+	size_t scratch_bytes, void* stream);
+
 /* Exclusive prefix sum of n uint32 values: out[i] = in[0] + ... + in[i-1]; *total (optional,
  * device) receives the sum of all n. Replaces the cub::DeviceScan::InclusiveSum over
  * tiles_touched and its temp-storage size query (cuda_rasterizer/rasterizer_impl.cu:166,277):

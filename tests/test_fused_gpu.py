@@ -85,3 +85,45 @@ def test_event_loss_kernel_vs_numpy_oracle_and_golden(cuda_dev):
     assert abs(o1[0].item() - o2[0].item()) < 1e-7
     assert rel_err((2 * s1["image_now"]).cpu().numpy(), s2["image_now"].cpu().numpy()) < 1e-6
     assert abs(2 * o1[1].item() - o2[1].item()) <= 1e-6 * abs(o2[1].item())
+
+
+def test_dist2_matches_bruteforce_oracle(cuda_dev):
+    """distCUDA2 replacement against the exact brute-force oracle (parity unpinned by the reference:
+    simple-knn is not in its tree)."""
+    from event_3dgs_b200.knn import distCUDA2
+    from oracle import raster_oracle as ro
+    rng = np.random.default_rng(0)
+    cases = {
+        "uniform": rng.uniform(-1.3, 1.3, (20_000, 3)),
+        "clustered": np.concatenate([rng.normal(0, 0.05, (6000, 3)), rng.normal(2, 0.5, (6000, 3)), rng.uniform(-20, 20, (50, 3))]),
+        "planar": np.concatenate([rng.uniform(-1, 1, (5000, 2)), np.full((5000, 1), 0.25)], 1),
+        "line": np.stack([np.linspace(0, 1, 3000), np.zeros(3000), np.zeros(3000)], 1),
+        "duplicates": np.repeat(rng.uniform(-1, 1, (500, 3)), 4, 0),
+        "five": rng.uniform(-1, 1, (5, 3)),
+        "four": rng.uniform(-1, 1, (4, 3)),
+    }
+    for name, pts in cases.items():
+        pts = pts.astype(np.float32)
+        got = distCUDA2(torch.as_tensor(pts).to(cuda_dev)).cpu().numpy()
+        ref = ro.dist2(pts)
+        assert got.shape == ref.shape
+        assert rel_err(got, ref, 1e-12) < 1e-5, name
+        # element-wise too (the scale init takes log(sqrt(.)) of every entry, gaussian_model.py:135)
+        assert np.allclose(got, ref, rtol=1e-4, atol=1e-12), name
+    # fewer than 4 points: FLT_MAX terms survive in the mean (overflow to inf), like the brute force
+    for n in (1, 2, 3):
+        pts = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+        got = distCUDA2(torch.as_tensor(pts).to(cuda_dev)).cpu().numpy()
+        ref = ro.dist2(pts)
+        assert np.array_equal(np.isinf(got), np.isinf(ref)) and (got[~np.isinf(got)] > 1e30).all()
+    assert distCUDA2(torch.zeros(0, 3, device=cuda_dev)).shape == (0,)
+    # 1M points (the size of a large COLMAP cloud): every value is finite, positive and consistent
+    # with a brute-force check on a sample
+    pts = rng.uniform(-1.3, 1.3, (1_000_000, 3)).astype(np.float32)
+    got = distCUDA2(torch.as_tensor(pts).to(cuda_dev)).cpu().numpy()
+    assert np.isfinite(got).all() and (got > 0).all()
+    idx = rng.choice(1_000_000, 200, replace=False)
+    D = ((pts[idx, None, :].astype(np.float64) - pts[None, :, :]) ** 2).sum(-1)
+    D[np.arange(200), idx] = np.inf
+    ref = np.sort(np.partition(D, 3, axis=1)[:, :3], 1).mean(1)
+    assert np.allclose(got[idx], ref, rtol=1e-4)
