@@ -18,6 +18,9 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+# NCCL prints its version banner on stdout at VERSION/INFO level; stdout carries ONE JSON line
+if os.environ.get("E3_KEEP_NCCL_DEBUG") is None:
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 import numpy as np  # noqa: E402
 
@@ -283,7 +286,9 @@ def main():
             loss.backward()
         if world > 1 and sync_grads:
             from event_3dgs_b200 import parallel
-            parallel.allreduce_gradients(leaves, world)
+            # at SH degree 0 the fused path knows d(features_rest) == 0 on every rank: nothing to exchange
+            skip_rest = use_fused and pc.active_sh_degree == 0
+            parallel.allreduce_gradients([p for p in leaves if not (skip_rest and p is pc._features_rest)], world)
         return loss
 
     def timed(fn, steps):
