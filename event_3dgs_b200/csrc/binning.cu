@@ -105,47 +105,71 @@ __global__ void __launch_bounds__(E3_SCAN_THREADS) scan_down_kernel(const uint32
 	}
 }
 
-// ---------------- LSD radix sort, one digit per pass ----------------
-// counts layout: counts[digit * nblk + block]  (digit-major, so one exclusive scan of the whole
-// array yields every block's output base for every digit)
-__global__ void __launch_bounds__(E3_SORT_THREADS) radix_hist_kernel(const uint32_t* __restrict__ keys, size_t n,
-	int shift, uint32_t mask, uint32_t* __restrict__ counts, uint32_t nblk)
+// ---------------- LSD radix sort, "onesweep" style ----------------
+// One histogram kernel for all passes, then ONE kernel per pass: every block ranks its tile
+// locally, obtains the number of equal digits in all earlier tiles by decoupled look-back
+// (single-word flag|count descriptors), reorders the tile in shared memory and writes each digit
+// run to global memory with consecutive threads on consecutive addresses. Stable.
+// Scratch (uint32 words): ghist[4][256] | tile_counter[8] | lookback[npass][ntiles][256].
+#define E3_LB_AGG 0x40000000u
+#define E3_LB_PREFIX 0x80000000u
+#define E3_LB_MASK 0x3fffffffu
+
+struct RadixPlan { int npass; int shift[4]; int bits[4]; };
+
+__global__ void __launch_bounds__(256) radix_hist_all_kernel(const uint32_t* __restrict__ keys, size_t n, RadixPlan plan,
+	uint32_t* __restrict__ ghist)
 {
-	__shared__ uint32_t hist[256];
-	hist[threadIdx.x] = 0;
+	__shared__ uint32_t hist[4][256];
+	for (int i = threadIdx.x; i < 4 * 256; i += 256) (&hist[0][0])[i] = 0;
 	__syncthreads();
-	const size_t start = (size_t)blockIdx.x * E3_SORT_TILE;
-	const size_t end = min(n, start + E3_SORT_TILE);
-	const int lane = threadIdx.x & 31;
-	for (size_t k = start + threadIdx.x; k < start + E3_SORT_TILE; k += E3_SORT_THREADS) {
-		const bool valid = k < end;
-		const uint32_t d = valid ? ((keys[k] >> shift) & mask) : 0xffffu;
-		// warp-aggregate equal digits (neighbouring instances often share a tile)
-		const uint32_t peers = __match_any_sync(E3_FULL, d);
-		if (valid && lane == (__ffs(peers) - 1)) atomicAdd(&hist[d], __popc(peers));
+	for (size_t k = (size_t)blockIdx.x * 256 + threadIdx.x; k < n; k += (size_t)gridDim.x * 256) {
+		const uint32_t key = keys[k];
+#pragma unroll
+		for (int p = 0; p < 4; p++)
+			if (p < plan.npass) atomicAdd(&hist[p][(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u)], 1u);
 	}
 	__syncthreads();
-	if (threadIdx.x <= mask) counts[(size_t)threadIdx.x * nblk + blockIdx.x] = hist[threadIdx.x];
+	for (int p = 0; p < plan.npass; p++) {
+		const uint32_t c = hist[p][threadIdx.x];
+		if (c) atomicAdd(&ghist[p * 256 + threadIdx.x], c);
+	}
 }
 
-__global__ void __launch_bounds__(E3_SORT_THREADS) radix_scatter_kernel(const uint32_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
 	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ bases, uint32_t nblk)
+	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist, volatile uint32_t* lookback,
+	uint32_t* __restrict__ tile_counter)
 {
 	__shared__ uint32_t wcnt[8][256];
+	__shared__ uint32_t s_keys[E3_SORT_TILE];
+	__shared__ uint32_t s_vals[E3_SORT_TILE];
+	__shared__ uint32_t s_gpos[256];      // global position of the first element of each digit run of this tile
+	__shared__ uint32_t s_lstart[256];    // position of that run inside the tile
+	__shared__ uint32_t s_warp[9];
+	__shared__ uint32_t s_tile;
+	if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1u);
 	for (int i = threadIdx.x; i < 8 * 256; i += E3_SORT_THREADS) (&wcnt[0][0])[i] = 0;
 	__syncthreads();
+	const uint32_t tile = s_tile;
 	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 	const uint32_t lt = (1u << lane) - 1u;
-	const size_t wstart = (size_t)blockIdx.x * E3_SORT_TILE + (size_t)w * (32 * E3_SORT_ITEMS);
-	uint32_t key[E3_SORT_ITEMS];
+	const size_t tstart = (size_t)tile * E3_SORT_TILE;
+	const size_t wstart = tstart + (size_t)w * (32 * E3_SORT_ITEMS);
+	const uint32_t tcount = (uint32_t)min((size_t)E3_SORT_TILE, n - tstart);
+	uint32_t key[E3_SORT_ITEMS], val[E3_SORT_ITEMS];
 	uint16_t rank[E3_SORT_ITEMS];
-	// items are taken in index order (warp, round, lane), so equal digits keep their order
 #pragma unroll
 	for (int i = 0; i < E3_SORT_ITEMS; i++) {
 		const size_t k = wstart + (size_t)i * 32 + lane;
 		const bool valid = k < n;
 		key[i] = valid ? keys_in[k] : 0xffffffffu;
+		val[i] = valid ? vals_in[k] : 0u;
+	}
+	// items are ranked in index order (warp, round, lane), so equal digits keep their order
+#pragma unroll
+	for (int i = 0; i < E3_SORT_ITEMS; i++) {
+		const bool valid = wstart + (size_t)i * 32 + lane < n;
 		const uint32_t d = valid ? ((key[i] >> shift) & mask) : 0xffffu;
 		const uint32_t peers = __match_any_sync(E3_FULL, d);
 		const int leader = __ffs(peers) - 1;
@@ -156,22 +180,50 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_scatter_kernel(const ui
 		__syncwarp();
 	}
 	__syncthreads();
-	// per digit: exclusive scan over the 8 warps, seeded with this block's global base
-	if (threadIdx.x <= mask) {
-		uint32_t run = bases[(size_t)threadIdx.x * nblk + blockIdx.x];
+	// per digit (thread d): tile total, look-back over earlier tiles, warp offsets
+	uint32_t total = 0;
+	const bool mine = threadIdx.x <= mask;
+	if (mine) {
 #pragma unroll
-		for (int ww = 0; ww < 8; ww++) { const uint32_t c = wcnt[ww][threadIdx.x]; wcnt[ww][threadIdx.x] = run; run += c; }
+		for (int ww = 0; ww < 8; ww++) { const uint32_t c = wcnt[ww][threadIdx.x]; wcnt[ww][threadIdx.x] = total; total += c; }
+		volatile uint32_t* my = lookback + (size_t)tile * 256 + threadIdx.x;
+		*my = total | (tile == 0 ? E3_LB_PREFIX : E3_LB_AGG);
+	}
+	// exclusive scans over the digits: global bases from the histogram, local run starts from the totals
+	uint32_t tot_all;
+	const uint32_t gb = block_excl_scan(mine ? ghist[threadIdx.x] : 0u, s_warp, tot_all);
+	const uint32_t ls = block_excl_scan(total, s_warp, tot_all);
+	if (mine) {
+		uint32_t excl = 0;
+		for (int t = (int)tile - 1; t >= 0; t--) {
+			volatile uint32_t* p = lookback + (size_t)t * 256 + threadIdx.x;
+			uint32_t v;
+			while (((v = *p) & (E3_LB_AGG | E3_LB_PREFIX)) == 0) __nanosleep(20);
+			excl += v & E3_LB_MASK;
+			if (v & E3_LB_PREFIX) break;
+		}
+		if (tile != 0) { __threadfence(); lookback[(size_t)tile * 256 + threadIdx.x] = (excl + total) | E3_LB_PREFIX; }
+		s_gpos[threadIdx.x] = gb + excl;
+		s_lstart[threadIdx.x] = ls;
 	}
 	__syncthreads();
+	// reorder the tile in shared memory: digit runs, original order inside a run
 #pragma unroll
 	for (int i = 0; i < E3_SORT_ITEMS; i++) {
-		const size_t k = wstart + (size_t)i * 32 + lane;
-		if (k < n) {
+		if (wstart + (size_t)i * 32 + lane < n) {
 			const uint32_t d = (key[i] >> shift) & mask;
-			const uint32_t pos = wcnt[w][d] + rank[i];
-			keys_out[pos] = key[i];
-			vals_out[pos] = vals_in[k];
+			const uint32_t lp = s_lstart[d] + wcnt[w][d] + rank[i];
+			s_keys[lp] = key[i];
+			s_vals[lp] = val[i];
 		}
+	}
+	__syncthreads();
+	for (uint32_t i = threadIdx.x; i < tcount; i += E3_SORT_THREADS) {
+		const uint32_t k = s_keys[i];
+		const uint32_t d = (k >> shift) & mask;
+		const uint32_t pos = s_gpos[d] + (i - s_lstart[d]);
+		keys_out[pos] = k;
+		vals_out[pos] = s_vals[i];
 	}
 }
 
@@ -250,26 +302,34 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
 	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st)
 {
+	(void)scan_tmp;
 	int cur = start_buf;
 	if (n > 0 && end_bit > 0) {
-		const int npass = (end_bit + 7) / 8;
+		RadixPlan plan;
+		plan.npass = e3_radix_passes(end_bit);
 		const size_t nblk = e3_sort_blocks(n);
 		int lo = 0;
-		for (int p = 0; p < npass; p++) {
+		for (int p = 0; p < 4; p++) { plan.shift[p] = 0; plan.bits[p] = 1; }
+		for (int p = 0; p < plan.npass; p++) {
 			// split the bits evenly over the passes (e.g. 12 -> 6 + 6): fewer digits per pass
-			// means longer contiguous runs per block in the scatter
-			const int nb = (end_bit - lo + (npass - p) - 1) / (npass - p);
-			const uint32_t mask = (1u << nb) - 1u;
-			const size_t nc = (size_t)(mask + 1) * nblk;
-			radix_hist_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], n, lo, mask, counts, (uint32_t)nblk);
-			cudaError_t e = e3_exclusive_scan_u32(counts, nullptr, counts, nc, scan_tmp, nullptr, st);
-			if (e != cudaSuccess) return e;
-			radix_scatter_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1],
-				vals[cur ^ 1], n, lo, mask, counts, (uint32_t)nblk);
-			g_e3_launches += 2;
-			cur ^= 1;
+			// means longer contiguous runs per tile in the scatter
+			const int nb = (end_bit - lo + (plan.npass - p) - 1) / (plan.npass - p);
+			plan.shift[p] = lo; plan.bits[p] = nb;
 			lo += nb;
 		}
+		uint32_t* ghist = counts;
+		uint32_t* tile_counter = counts + 4 * 256;
+		uint32_t* lookback = counts + 4 * 256 + 8;
+		cudaError_t e = cudaMemsetAsync(counts, 0, e3_sort_scratch_words(n) * sizeof(uint32_t), st);
+		if (e != cudaSuccess) return e;
+		const unsigned hgrid = (unsigned)(nblk < 1184 ? nblk : 1184);
+		radix_hist_all_kernel<<<hgrid, 256, 0, st>>>(keys[cur], n, plan, ghist);
+		for (int p = 0; p < plan.npass; p++) {
+			radix_onesweep_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
+				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * nblk * 256, tile_counter + p);
+			cur ^= 1;
+		}
+		g_e3_launches += 1 + plan.npass;
 	}
 	*result_buf = cur;
 	return cudaGetLastError();

@@ -34,6 +34,8 @@ static inline void e3_carve(char*& p, T*& out, size_t count)
 #define E3_SCAN_TILE (E3_SCAN_THREADS * E3_SCAN_ITEMS)
 
 static inline size_t e3_sort_blocks(size_t n) { return (n + E3_SORT_TILE - 1) / E3_SORT_TILE; }
+// uint32 words of radix-sort scratch: 4 global histograms, tile counters, look-back descriptors of 4 passes
+static inline size_t e3_sort_scratch_words(size_t n) { return 4 * 256 + 8 + 4 * e3_sort_blocks(n) * 256; }
 static inline size_t e3_scan_blocks(size_t n) { return (n + E3_SCAN_TILE - 1) / E3_SCAN_TILE; }
 
 struct E3GeomState {
@@ -47,8 +49,8 @@ struct E3GeomState {
 	uint32_t* dkey[2];        // [P] depth keys, ping-pong
 	uint32_t* dval[2];        // [P] Gaussian ids in depth order, ping-pong
 	uint32_t* offsets;        // [P] exclusive instance offsets in depth order
-	uint32_t* sort_counts;    // [256 * sort_blocks(P)]
-	uint32_t* scan_tmp;       // [max(scan_blocks(256*sort_blocks(P)), scan_blocks(P)) + 2]
+	uint32_t* sort_counts;    // [e3_sort_scratch_words(P)]
+	uint32_t* scan_tmp;       // [scan_blocks(P) + 2]
 	float* acc;               // [P * E3_ACC_STRIDE] backward accumulators
 	int* flags;               // [4]: 0 num_rendered, 1 prefiltered-violation
 	static E3GeomState carve(char* p, size_t P, char** end = nullptr)
@@ -66,10 +68,8 @@ struct E3GeomState {
 		e3_carve(p, s.dval[0], P);
 		e3_carve(p, s.dval[1], P);
 		e3_carve(p, s.offsets, P);
-		size_t nc = 256 * e3_sort_blocks(P);
-		e3_carve(p, s.sort_counts, nc);
-		size_t nt = e3_scan_blocks(nc) > e3_scan_blocks(P) ? e3_scan_blocks(nc) : e3_scan_blocks(P);
-		e3_carve(p, s.scan_tmp, nt + 2);
+		e3_carve(p, s.sort_counts, e3_sort_scratch_words(P));
+		e3_carve(p, s.scan_tmp, e3_scan_blocks(P) + 2);
 		e3_carve(p, s.acc, P * E3_ACC_STRIDE);
 		e3_carve(p, s.flags, 4);
 		if (end) *end = p;
@@ -95,8 +95,8 @@ struct E3ImageState {
 struct E3BinState {
 	uint32_t* tkey[2];      // [R] tile ids, ping-pong
 	uint32_t* val[2];       // [R] Gaussian ids, ping-pong
-	uint32_t* sort_counts;  // [256 * sort_blocks(R)]
-	uint32_t* scan_tmp;     // [scan_blocks(256*sort_blocks(R)) + 2]
+	uint32_t* sort_counts;  // [e3_sort_scratch_words(R)]
+	uint32_t* scan_tmp;     // unused
 	static E3BinState carve(char* p, size_t R, char** end = nullptr)
 	{
 		E3BinState s;
@@ -104,9 +104,8 @@ struct E3BinState {
 		e3_carve(p, s.tkey[1], R);
 		e3_carve(p, s.val[0], R);
 		e3_carve(p, s.val[1], R);
-		size_t nc = 256 * e3_sort_blocks(R);
-		e3_carve(p, s.sort_counts, nc);
-		e3_carve(p, s.scan_tmp, e3_scan_blocks(nc) + 2);
+		e3_carve(p, s.sort_counts, e3_sort_scratch_words(R));
+		e3_carve(p, s.scan_tmp, 8);
 		if (end) *end = p;
 		return s;
 	}

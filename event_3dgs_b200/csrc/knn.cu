@@ -150,8 +150,7 @@ size_t e3_knn_scratch_layout(int P, uint32_t** keys, uint32_t** vals, uint32_t**
 	char* p = base;
 	uint32_t *k0, *k1, *v0, *v1, *cn, *stp, *bb; uint2* rg; float4* so; KnnGrid* gr;
 	e3_carve(p, k0, (size_t)P); e3_carve(p, k1, (size_t)P); e3_carve(p, v0, (size_t)P); e3_carve(p, v1, (size_t)P);
-	const size_t nc = 256 * e3_sort_blocks((size_t)P);
-	e3_carve(p, cn, nc); e3_carve(p, stp, e3_scan_blocks(nc) + 2);
+	e3_carve(p, cn, e3_sort_scratch_words((size_t)P)); e3_carve(p, stp, 8);
 	e3_carve(p, rg, ncell); e3_carve(p, so, (size_t)P); e3_carve(p, bb, 8); e3_carve(p, gr, 1);
 	if (keys) { keys[0] = k0; keys[1] = k1; vals[0] = v0; vals[1] = v1; *counts = cn; *scan_tmp = stp; *ranges = rg; *sorted = so; *bbox = bb; *grid = gr; }
 	return (size_t)(p - base) + 256;

@@ -383,7 +383,7 @@ __device__ __forceinline__ void put(float* p, float v) { if (ACC) *p += v; else 
 // dL_dopacity = d opacity logit, dL_dscale = d log-scale, dL_drot = d raw quaternion,
 // dL_dmean2D optional, dL_dcolor / dL_dcov3D / dL_dconic unused (NULL).
 template <int C, bool RAW, bool ACC>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(
+__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 	int P, int D, int M,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ f_rest, float* __restrict__ d_frest, const float* __restrict__ opacities_raw,

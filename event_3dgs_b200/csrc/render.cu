@@ -256,7 +256,9 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 #pragma unroll
 			for (int i = 0; i < 8; i++) v[i] = 0.f;
 			if (valid) {
-				T = T / (1.f - alpha);
+				// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path)
+				const float ra = __frcp_rn(1.f - alpha);
+				T = T * ra;
 				const float dchannel_dcolor = alpha * T;
 				float col[3];
 				col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? sC[j] : 0.f;
@@ -269,7 +271,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 				}
 				dL_dalpha *= T;
 				last_alpha = alpha;
-				dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+				dL_dalpha += (-T_final * ra) * bg_dot_dpixel;
 				const float dL_dG = b.y * dL_dalpha;
 				const float gdx = G * dx, gdy = G * dy;
 				const float dG_ddelx = -gdx * a.z - gdy * a.w;
