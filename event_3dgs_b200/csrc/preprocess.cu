@@ -374,16 +374,40 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 template <bool ACC>
 __device__ __forceinline__ void put(float* p, float v) { if (ACC) *p += v; else *p = v; }
 
+// coalesced write-out of a staged [rows,K] tile (float4 where the global row start is aligned)
+template <bool ACC>
+__device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float* sm, int nfl)
+{
+	if ((reinterpret_cast<size_t>(dst) & 15) == 0) {
+		const int nv = nfl >> 2;
+		float4* d4 = reinterpret_cast<float4*>(dst);
+		const float4* s4 = reinterpret_cast<const float4*>(sm);
+		for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+			float4 v = s4[i];
+			if (ACC) { const float4 o = d4[i]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+			d4[i] = v;
+		}
+		for (int i = (nv << 2) + threadIdx.x; i < nfl; i += blockDim.x) dst[i] = ACC ? dst[i] + sm[i] : sm[i];
+	} else {
+		for (int i = threadIdx.x; i < nfl; i += blockDim.x) dst[i] = ACC ? dst[i] + sm[i] : sm[i];
+	}
+}
+
+#define E3_PB_THREADS 128
+
 // RAW: gradients are taken all the way to the leaf parameters (chain rule through exp /
 // normalize / sigmoid and the SH evaluation, i.e. the autograd backward of K15 in SURVEY.md 2b).
 // ACC: add to the output rows instead of overwriting them (renders 2 and 3 of an event iteration
-// accumulate into the gradient tensors written by render 1); rows of culled Gaussians are then
-// left untouched. Pointer roles in RAW mode: shs = features_dc [P,3], f_rest = features_rest
-// [P,15,3], dL_dsh = d features_dc, d_frest = d features_rest (NULL when D == 0: identically 0),
-// dL_dopacity = d opacity logit, dL_dscale = d log-scale, dL_drot = d raw quaternion,
-// dL_dmean2D optional, dL_dcolor / dL_dcov3D / dL_dconic unused (NULL).
-template <int C, bool RAW, bool ACC>
-__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
+// accumulate into the gradient tensors written by render 1). SHREST: features_rest and its
+// gradient are staged through shared memory as [128,45] tiles (RAW with degree > 0).
+// Pointer roles in RAW mode: shs = features_dc [P,3], f_rest = features_rest [P,15,3],
+// dL_dsh = d features_dc, d_frest = d features_rest, dL_dopacity = d opacity logit,
+// dL_dscale = d log-scale, dL_drot = d raw quaternion, dL_dmean2D optional,
+// dL_dcolor / dL_dcov3D / dL_dconic unused (NULL).
+// All 12-byte-row inputs and outputs go through shared memory so that global traffic is
+// 16-byte vectorised and fully coalesced (a thread-per-row access pattern has stride 12/180 B).
+template <int C, bool RAW, bool ACC, bool SHREST>
+__global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	int P, int D, int M,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ f_rest, float* __restrict__ d_frest, const float* __restrict__ opacities_raw,
@@ -396,57 +420,100 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 	float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
 	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
 {
-	__shared__ float s_m[32];
+	constexpr int BT = E3_PB_THREADS;
+	extern __shared__ __align__(16) float smem[];
+	float* s_mean = smem;               // in: means3D rows   -> out: d means3D
+	float* s_scl = s_mean + BT * 3;     // in: scale rows     -> out: d scale
+	float* s_fdc = s_scl + BT * 3;      // in: features_dc    -> out: d features_dc (RAW)
+	float* s_cov = s_fdc + BT * 3;      // in: cov3D rows [BT*6] -> out: d mean2D [BT*3]
+	float* s_m = s_cov + BT * 6;        // view + proj matrices [32]
+	float* s_sh = s_m + 32;             // in: features_rest tile [BT*45] (SHREST)
+	float* s_dsh = s_sh + BT * 45;      // out: d features_rest tile [BT*45] (SHREST)
+	const size_t first = (size_t)blockIdx.x * BT;
+	const int rows = min(BT, P - (int)first);
+	const int t = threadIdx.x;
+	const bool live = t < rows;
+	const size_t idx = first + (live ? t : 0);
+	// Issue EVERY global load of this thread before the first barrier, whether or not the
+	// Gaussian turns out to be visible: one round trip to memory instead of a chain of
+	// dependent ones (the kernel is latency bound, not bandwidth bound).
+	int rad = 0;
+	float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, a2 = a0;
+	float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+	float opac_raw = 0.f;
+	uint8_t cl[3] = { 0, 0, 0 };
+	float4* a4 = reinterpret_cast<float4*>(acc + idx * E3_ACC_STRIDE);
+	if (live) {
+		rad = radii[idx];
+		a0 = a4[0]; a1 = a4[1]; a2 = a4[2];
+		if (scales) q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+		if (RAW) opac_raw = __ldg(opacities_raw + idx);
+		if (shs) { cl[0] = clamped[3 * idx]; cl[1] = clamped[3 * idx + 1]; cl[2] = clamped[3 * idx + 2]; }
+	}
+	stage_rows<3>(means3D, first, rows, s_mean);
+	if (scales) stage_rows<3>(scales, first, rows, s_scl);
+	if (RAW) stage_rows<3>(shs, first, rows, s_fdc);
+	stage_rows<6>(cov3D_precomp ? cov3D_precomp : cov3D_state, first, rows, s_cov);
+	if (SHREST) stage_rows<45>(f_rest, first, rows, s_sh);
 	if (threadIdx.x < 16) s_m[threadIdx.x] = vm_g[threadIdx.x];
 	else if (threadIdx.x < 32) s_m[threadIdx.x] = pm_g[threadIdx.x - 16];
 	__syncthreads();
-	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= (size_t)P) return;
 	const float* vm = s_m;
 	const float* proj = s_m + 16;
-	const bool vis = radii[idx] > 0;
-
-	float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, a2 = a0;
+	const bool vis = live && rad > 0;
 	if (vis) {
-		float4* a4 = reinterpret_cast<float4*>(acc + idx * E3_ACC_STRIDE);
-		a0 = a4[0]; a1 = a4[1]; a2 = a4[2];
 		// leave the accumulator clean so that a second backward of the same forward is correct
 		a4[0] = a4[1] = a4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-	}
-	if (ACC && !vis) return;
-	// outputs that are plain copies of the accumulators
-	if (dL_dmean2D) { put<ACC>(dL_dmean2D + 3 * idx, a0.x); put<ACC>(dL_dmean2D + 3 * idx + 1, a0.y); if (!ACC) dL_dmean2D[3 * idx + 2] = 0.f; }
-	if (dL_dconic) reinterpret_cast<float4*>(dL_dconic)[idx] = make_float4(a0.z, a0.w, 0.f, a1.x);
-	const float dcol[3] = { a1.z, a1.w, a2.x };
-	if (!RAW) {
-		dL_dopacity[idx] = a1.y;
-#pragma unroll
-		for (int c = 0; c < C; c++) dL_dcolor[idx * C + c] = dcol[c];
 	} else {
-		// sigmoid backward (gaussian_model.py:31): d logit = d opacity * o * (1 - o)
-		float dlogit = 0.f;
-		if (vis) { const float o = 1.0f / (1.0f + expf(-__ldg(opacities_raw + idx))); dlogit = a1.y * o * (1.0f - o); }
-		put<ACC>(dL_dopacity + idx, dlogit);
+		a0 = a1 = a2 = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
+	const float3 mean = make_float3(s_mean[3 * t], s_mean[3 * t + 1], s_mean[3 * t + 2]);
+	float c3[6];
+#pragma unroll
+	for (int i = 0; i < 6; i++) c3[i] = s_cov[6 * t + i];
+	float sact[3] = { 1.f, 1.f, 1.f };
+	if (scales) { sact[0] = s_scl[3 * t]; sact[1] = s_scl[3 * t + 1]; sact[2] = s_scl[3 * t + 2]; }
+	float fdc[3] = { 0.f, 0.f, 0.f };
+	if (RAW) { fdc[0] = s_fdc[3 * t]; fdc[1] = s_fdc[3 * t + 1]; fdc[2] = s_fdc[3 * t + 2]; }
+	__syncthreads();          // every staged input row is in registers: the buffers now carry outputs
+
+	const float dcol[3] = { a1.z, a1.w, a2.x };
+	if (live) {
+		if (dL_dconic) reinterpret_cast<float4*>(dL_dconic)[idx] = make_float4(a0.z, a0.w, 0.f, a1.x);
+		if (!RAW) {
+			dL_dopacity[idx] = a1.y;
+#pragma unroll
+			for (int c = 0; c < C; c++) dL_dcolor[idx * C + c] = dcol[c];
+		} else {
+			// sigmoid backward (gaussian_model.py:31): d logit = d opacity * o * (1 - o)
+			float dlogit = 0.f;
+			if (vis) { const float o = 1.0f / (1.0f + expf(-opac_raw)); dlogit = a1.y * o * (1.0f - o); }
+			if (!ACC || vis) put<ACC>(dL_dopacity + idx, dlogit);
+		}
+	}
+	s_cov[3 * t] = a0.x; s_cov[3 * t + 1] = a0.y; s_cov[3 * t + 2] = 0.f;      // d mean2D row
 
 	float3 dmean = make_float3(0, 0, 0);
 	float dcov[6] = { 0, 0, 0, 0, 0, 0 };
+	float dfdc[3] = { 0.f, 0.f, 0.f };
+	if (SHREST) {
+		float* row = s_dsh + 45 * t;
+		for (int k = 0; k < 45; k++) row[k] = 0.f;
+	}
 	if (vis) {
-		const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
-		const float* c3 = (cov3D_precomp ? cov3D_precomp : cov3D_state) + 6 * idx;
 		const float dcx = a0.z, dcy = a0.w, dcz = a1.x;
 		// ---- computeCov2DCUDA, backward.cu:166-273 ----
-		float3 t = make_float3(vm[0] * mean.x + vm[4] * mean.y + vm[8] * mean.z + vm[12],
+		float3 tt = make_float3(vm[0] * mean.x + vm[4] * mean.y + vm[8] * mean.z + vm[12],
 			vm[1] * mean.x + vm[5] * mean.y + vm[9] * mean.z + vm[13],
 			vm[2] * mean.x + vm[6] * mean.y + vm[10] * mean.z + vm[14]);
 		const float limx = 1.3f * tan_fovx, limy = 1.3f * tan_fovy;
-		const float txtz = t.x / t.z, tytz = t.y / t.z;
-		t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
-		t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
+		const float txtz = tt.x / tt.z, tytz = tt.y / tt.z;
+		tt.x = fminf(limx, fmaxf(-limx, txtz)) * tt.z;
+		tt.y = fminf(limy, fmaxf(-limy, tytz)) * tt.z;
 		const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
 		const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
-		const float ja = h_x / t.z, jc = -(h_x * t.x) / (t.z * t.z);
-		const float jb = h_y / t.z, jd = -(h_y * t.y) / (t.z * t.z);
+		const float ja = h_x / tt.z, jc = -(h_x * tt.x) / (tt.z * tt.z);
+		const float jb = h_y / tt.z, jd = -(h_y * tt.y) / (tt.z * tt.z);
 		float T[2][3], Wm[3][3];    // glm T[c][r], W[k][r] = vm[4r+k]
 #pragma unroll
 		for (int r = 0; r < 3; r++) {
@@ -489,10 +556,10 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 		const float dL_dJ02 = Wm[2][0] * dT0[0] + Wm[2][1] * dT0[1] + Wm[2][2] * dT0[2];
 		const float dL_dJ11 = Wm[1][0] * dT1[0] + Wm[1][1] * dT1[1] + Wm[1][2] * dT1[2];
 		const float dL_dJ12 = Wm[2][0] * dT1[0] + Wm[2][1] * dT1[1] + Wm[2][2] * dT1[2];
-		const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+		const float tz = 1.f / tt.z, tz2 = tz * tz, tz3 = tz2 * tz;
 		const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
 		const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-		const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 + (2 * h_y * t.y) * tz3 * dL_dJ12;
+		const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * tt.x) * tz3 * dL_dJ02 + (2 * h_y * tt.y) * tz3 * dL_dJ12;
 		dmean.x = vm[0] * dL_dtx + vm[1] * dL_dty + vm[2] * dL_dtz;
 		dmean.y = vm[4] * dL_dtx + vm[5] * dL_dty + vm[6] * dL_dtz;
 		dmean.z = vm[8] * dL_dtx + vm[9] * dL_dty + vm[10] * dL_dtz;
@@ -507,22 +574,19 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 		dmean.z += (proj[8] * m_w - proj[11] * mul1) * gx2 + (proj[9] * m_w - proj[11] * mul2) * gy2;
 		if (shs) {
 			if (RAW)
-				sh_backward<ACC>(D, 16, shs + idx * 3, f_rest ? f_rest + idx * 45 : nullptr, mean.x - campos[0], mean.y - campos[1],
-					mean.z - campos[2], clamped + 3 * idx, dcol, dL_dsh + idx * 3, d_frest ? d_frest + idx * 45 : nullptr, dmean);
+				sh_backward<false>(D, 16, fdc, SHREST ? s_sh + 45 * t : (f_rest ? f_rest + idx * 45 : nullptr), mean.x - campos[0],
+					mean.y - campos[1], mean.z - campos[2], cl, dcol, dfdc,
+					SHREST ? s_dsh + 45 * t : nullptr, dmean);
 			else
 				sh_backward<false>(D, M, shs + idx * M * 3, shs + idx * M * 3 + 3, mean.x - campos[0], mean.y - campos[1],
-					mean.z - campos[2], clamped + 3 * idx, dcol, dL_dsh + idx * M * 3, dL_dsh + idx * M * 3 + 3, dmean);
+					mean.z - campos[2], cl, dcol, dL_dsh + idx * M * 3, dL_dsh + idx * M * 3 + 3, dmean);
 		}
-	} else if (shs && !ACC) {
-		if (RAW) {
-			dL_dsh[idx * 3] = dL_dsh[idx * 3 + 1] = dL_dsh[idx * 3 + 2] = 0.f;
-			if (d_frest) for (int k = 0; k < 45; k++) d_frest[idx * 45 + k] = 0.f;
-		} else {
-			for (int k = 0; k < 3 * M; k++) dL_dsh[idx * M * 3 + k] = 0.f;
-		}
+	} else if (live && shs && !RAW) {
+		for (int k = 0; k < 3 * M; k++) dL_dsh[idx * M * 3 + k] = 0.f;
 	}
-	put<ACC>(dL_dmean3D + 3 * idx, dmean.x); put<ACC>(dL_dmean3D + 3 * idx + 1, dmean.y); put<ACC>(dL_dmean3D + 3 * idx + 2, dmean.z);
-	if (dL_dcov3D) {
+	s_mean[3 * t] = dmean.x; s_mean[3 * t + 1] = dmean.y; s_mean[3 * t + 2] = dmean.z;
+	if (RAW) { s_fdc[3 * t] = dfdc[0]; s_fdc[3 * t + 1] = dfdc[1]; s_fdc[3 * t + 2] = dfdc[2]; }
+	if (live && dL_dcov3D) {
 #pragma unroll
 		for (int i = 0; i < 6; i++) dL_dcov3D[6 * idx + i] = dcov[i];
 	}
@@ -532,11 +596,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 		float ds[3] = { 0, 0, 0 };
 		float4 dq = make_float4(0, 0, 0, 0);
 		float qnorm_inv = 1.f;
-		float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
-		float sact[3] = { 1.f, 1.f, 1.f };
 		if (vis) {
-			q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
-			sact[0] = scales[3 * idx]; sact[1] = scales[3 * idx + 1]; sact[2] = scales[3 * idx + 2];
 			if (RAW) {
 				qnorm_inv = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
 				q.x *= qnorm_inv; q.y *= qnorm_inv; q.z *= qnorm_inv; q.w *= qnorm_inv;
@@ -571,20 +631,29 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(
 			dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
 			dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
 			dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
-		}
-		if (RAW) {
-			// exp backward: d log-scale = d scale * scale;  F.normalize backward:
-			// d raw = (d qhat - qhat (qhat . d qhat)) / |raw|
+			if (RAW) {
+				// exp backward: d log-scale = d scale * scale;  F.normalize backward:
+				// d raw = (d qhat - qhat (qhat . d qhat)) / |raw|
 #pragma unroll
-			for (int i = 0; i < 3; i++) ds[i] *= sact[i];
-			const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
-			dq.x = (dq.x - q.x * dot) * qnorm_inv; dq.y = (dq.y - q.y * dot) * qnorm_inv;
-			dq.z = (dq.z - q.z * dot) * qnorm_inv; dq.w = (dq.w - q.w * dot) * qnorm_inv;
+				for (int i = 0; i < 3; i++) ds[i] *= sact[i];
+				const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+				dq.x = (dq.x - q.x * dot) * qnorm_inv; dq.y = (dq.y - q.y * dot) * qnorm_inv;
+				dq.z = (dq.z - q.z * dot) * qnorm_inv; dq.w = (dq.w - q.w * dot) * qnorm_inv;
+			}
 		}
-		put<ACC>(dL_dscale + 3 * idx, ds[0]); put<ACC>(dL_dscale + 3 * idx + 1, ds[1]); put<ACC>(dL_dscale + 3 * idx + 2, ds[2]);
-		put<ACC>(dL_drot + 4 * idx, dq.x); put<ACC>(dL_drot + 4 * idx + 1, dq.y);
-		put<ACC>(dL_drot + 4 * idx + 2, dq.z); put<ACC>(dL_drot + 4 * idx + 3, dq.w);
+		s_scl[3 * t] = ds[0]; s_scl[3 * t + 1] = ds[1]; s_scl[3 * t + 2] = ds[2];
+		if (live && (!ACC || vis)) {
+			float4* dr = reinterpret_cast<float4*>(dL_drot) + idx;
+			if (ACC) { const float4 o = *dr; dq.x += o.x; dq.y += o.y; dq.z += o.z; dq.w += o.w; }
+			*dr = dq;
+		}
 	}
+	__syncthreads();
+	flush_rows<ACC>(dL_dmean3D + first * 3, s_mean, rows * 3);
+	if (scales) flush_rows<ACC>(dL_dscale + first * 3, s_scl, rows * 3);
+	if (RAW) flush_rows<ACC>(dL_dsh + first * 3, s_fdc, rows * 3);
+	if (dL_dmean2D) flush_rows<ACC>(dL_dmean2D + first * 3, s_cov, rows * 3);
+	if (SHREST) flush_rows<ACC>(d_frest + first * 45, s_dsh, rows * 45);
 }
 
 }  // namespace
@@ -621,13 +690,25 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* d_frest,
 	float* dL_dscale, float* dL_drot, cudaStream_t st)
 {
-	const int grid = (f.P + 255) / 256;
-#define LAUNCH(CH, RW, AC) preprocess_bwd_kernel<CH, RW, AC><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
+	constexpr int BT = E3_PB_THREADS;
+	const int grid = (f.P + BT - 1) / BT;
+	const bool shrest = raw && f.D > 0 && d_frest != nullptr;
+	const size_t smem_small = (size_t)(BT * 15 + 32) * sizeof(float);
+	const size_t smem_big = smem_small + (size_t)BT * 90 * sizeof(float);
+#define LAUNCH(CH, RW, AC, SR) do { \
+	auto kern = preprocess_bwd_kernel<CH, RW, AC, SR>; \
+	const size_t sm = SR ? smem_big : smem_small; \
+	static bool attr_set = false; \
+	if (SR && !attr_set) { cudaError_t ea = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); if (ea != cudaSuccess) return ea; attr_set = true; } \
+	kern<<<grid, BT, sm, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
-	dL_dscale, dL_drot)
-	if (raw) { if (accumulate) LAUNCH(3, true, true); else LAUNCH(3, true, false); }
-	else if (f.C == 1) LAUNCH(1, false, false); else LAUNCH(3, false, false);
+	dL_dscale, dL_drot); } while (0)
+	if (raw) {
+		if (shrest) { if (accumulate) LAUNCH(3, true, true, true); else LAUNCH(3, true, false, true); }
+		else { if (accumulate) LAUNCH(3, true, true, false); else LAUNCH(3, true, false, false); }
+	}
+	else if (f.C == 1) LAUNCH(1, false, false, false); else LAUNCH(3, false, false, false);
 #undef LAUNCH
 	g_e3_launches += 1;
 	return cudaGetLastError();
