@@ -186,15 +186,25 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 	__shared__ float s_scl[256 * 3];
 	__shared__ float s_col[256 * 3];
 	__shared__ float s_m[32];
+	extern __shared__ __align__(16) float s_shr[];      // [256*45] features_rest tile (RAW, degree > 0)
 	const size_t first = (size_t)blockIdx.x * 256;
 	const int rows = min(256, P - (int)first);
+	const int t = threadIdx.x;
+	// all per-thread global loads are issued before the barrier (one memory round trip)
+	float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+	float opac_in = 0.f;
+	if (t < rows) {
+		if (!cov3D_precomp) q_in = __ldg(reinterpret_cast<const float4*>(rotations) + first + t);
+		opac_in = __ldg(opacities + first + t);
+	}
 	stage_rows<3>(means3D, first, rows, s_xyz);
 	if (scales) stage_rows<3>(scales, first, rows, s_scl);
 	if (colors_precomp) stage_rows<C>(colors_precomp, first, rows, s_col);
+	const bool sh_tile = RAW && D > 0;
+	if (sh_tile) stage_rows<45>(f_rest, first, rows, s_shr);
 	if (threadIdx.x < 16) s_m[threadIdx.x] = vm_g[threadIdx.x];
 	else if (threadIdx.x < 32) s_m[threadIdx.x] = pm_g[threadIdx.x - 16];
 	__syncthreads();
-	const int t = threadIdx.x;
 	if (t >= rows) return;
 	const size_t idx = first + t;
 	const float* vm = s_m;
@@ -226,7 +236,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 #pragma unroll
 			for (int i = 0; i < 6; i++) c3[i] = cov3D_precomp[idx * 6 + i];
 		} else {
-			float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+			float4 q = q_in;
 			if (RAW) {    // rotation_activation = F.normalize (gaussian_model.py:36): x / max(|x|, 1e-12)
 				const float inv = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
 				q.x *= inv; q.y *= inv; q.z *= inv; q.w *= inv;
@@ -255,7 +265,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 		} else {
 			uint8_t cl[3];
 			const float* sh0 = RAW ? shs + idx * 3 : shs + idx * M * 3;
-			const float* shr = RAW ? f_rest + idx * 45 : sh0 + 3;
+			const float* shr = RAW ? (sh_tile ? s_shr + 45 * t : f_rest + idx * 45) : sh0 + 3;
 			const float3 v = sh_to_color(D, sh0, shr, px - campos[0], py - campos[1], pz - campos[2], cl);
 			col[0] = v.x; col[1] = v.y; col[2] = v.z;
 			rgb[idx * 3] = v.x; rgb[idx * 3 + 1] = v.y; rgb[idx * 3 + 2] = v.z;
@@ -270,7 +280,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 		// half-extent of the bounding box of { alpha >= 1/255 } = { power >= -ln(255 opacity) }:
 		// sqrt(2 tau cov_xx), sqrt(2 tau cov_yy) (cov = inverse of the conic). Margins make the
 		// box a strict superset under fp32 rounding of the blend's own power evaluation.
-		float opac = __ldg(opacities + idx);
+		float opac = opac_in;
 		if (RAW) opac = 1.0f / (1.0f + expf(-opac));      // opacity_activation = sigmoid
 		const float tau = __logf(255.0f * opac) + 1e-3f;
 		float ext_x = -1.f, ext_y = -1.f;
@@ -664,7 +674,16 @@ cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const f
 	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st)
 {
 	const int grid = (f.P + 255) / 256;
-#define LAUNCH(CH, RW) preprocess_fwd_kernel<CH, RW><<<grid, 256, 0, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
+	const size_t dyn = (raw && f.D > 0) ? (size_t)256 * 45 * sizeof(float) : 0;
+	if (dyn) {
+		static bool attr_set = false;
+		if (!attr_set) {
+			cudaError_t ea = cudaFuncSetAttribute(preprocess_fwd_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+			if (ea != cudaSuccess) return ea;
+			attr_set = true;
+		}
+	}
+#define LAUNCH(CH, RW) preprocess_fwd_kernel<CH, RW><<<grid, 256, dyn, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
 	rotations, opacities, shs, f_rest, cov3D_precomp, colors_precomp, viewmatrix, projmatrix, cam_pos, f.W, f.H, \
 	f.tan_fovx, f.tan_fovy, f.focal_x, f.focal_y, f.gx, f.gy, prefiltered, radii, g.depths, g.rec, g.cov3D, g.rgb, \
 	g.clamped, g.tiles_touched, g.rect, g.dkey[0], g.dval[0], g.acc, g.flags)
