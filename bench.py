@@ -392,6 +392,18 @@ def main():
     line["iter_roofline"] = {"algorithmic_bytes": b_iter, "achieved_gbs": b_iter / (ms_per_step * 1e-3) / 1e9,
                              "frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak}
     line["stages_ms_per_iter"] = stages
+    if use_fused:
+        # extra (not the headline): the reference's train and event camera lists share their poses
+        # (scene/dataset_readers.py:145-160), so the intensity view and the first event view are the
+        # same view; rendering it once is loss- and gradient-equivalent (fused.same_view)
+        def it_dedupe(s):
+            v = view_of(args.warmup + s)
+            fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt_dev, c_param, bg, deblur=deblur, dedupe_views=True)
+        for s in range(3):
+            it_dedupe(s)
+        ms_d, _, _ = timed(it_dedupe, args.steps)
+        line["dedupe_identical_views"] = {"value": world * 1e3 / (ms_d / args.steps), "unit": UNIT, "ms_per_step": ms_d / args.steps,
+                                          "note": "opt-in; 2 renders instead of 3 when train and event camera coincide; no gradient exchange in this extra"}
 
     if rank == 0 and world == 1:
         # reference CUDA build (oracle/_ref) on the same tensors, same timing window

@@ -179,7 +179,8 @@ static int forward_impl(
 	E3_STAGE(E3_STAGE_TILE_SORT, e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, tile_bits, b.sort_counts, b.scan_tmp, s0, &bres, st));
 	if (bres != 0) return E3_ERR_BAD_ARGUMENT;
 	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
-	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
+	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_order(im.ranges, (int)T, im.tile_order, st));
+	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
 	return 0;
 }
 
@@ -249,7 +250,7 @@ int e3_rasterize_backward(
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
 	if (R > 0) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
-		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
 	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, means3D, radii, shs, nullptr, nullptr, false, false, scales, rotations,
@@ -285,7 +286,7 @@ int e3_rasterize_backward_raw(
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
 	if (R > 0) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
-		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
 	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,

@@ -81,12 +81,14 @@ struct E3ImageState {
 	float* final_T;       // [N]
 	uint32_t* n_contrib;  // [N]
 	uint2* ranges;        // [T]
+	uint32_t* tile_order; // [T] tile ids, longest list first
 	static E3ImageState carve(char* p, size_t N, size_t T, char** end = nullptr)
 	{
 		E3ImageState s;
 		e3_carve(p, s.final_T, N);
 		e3_carve(p, s.n_contrib, N);
 		e3_carve(p, s.ranges, T);
+		e3_carve(p, s.tile_order, T);
 		if (end) *end = p;
 		return s;
 	}
@@ -152,10 +154,11 @@ cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_
 cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges, size_t T,
 	cudaStream_t st);
 
-cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges,
+cudaError_t e3_launch_tile_order(const uint2* ranges, int T, uint32_t* order, cudaStream_t st);
+cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, float* final_T,
 	uint32_t* n_contrib, float* out_color, cudaStream_t st);
-cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges,
+cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
 	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st);
 

@@ -56,24 +56,27 @@ __device__ __forceinline__ float eval_power(float dx, float dy, float cx, float 
 }
 
 template <int C>
-__global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict__ ranges,
-	const uint32_t* __restrict__ point_list, int W, int H, const float4* __restrict__ rec,
+__global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+	int gx, const uint32_t* __restrict__ point_list, int W, int H, const float4* __restrict__ rec,
 	const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
 	float* __restrict__ out_color)
 {
-	__shared__ float4 sA[kBatch];   // x, y, conic.x, conic.y
-	__shared__ float4 sB[kBatch];   // conic.z, opacity, c0, c1
+	// {x, y, conic.x, conic.y} and {conic.z, opacity, c0, c1} of instance j at sAB[2j], sAB[2j+1]:
+	// one address computation, two LDS.128 at fixed offsets
+	__shared__ float4 sAB[kBatch * 2];
 	__shared__ float sC[kBatch];    // c2
 	__shared__ uint8_t sMask[kBatch];
 	int lx, ly;
 	pixel_of_thread(lx, ly);
 	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-	const int px = blockIdx.x * E3_TILE_X + lx, py = blockIdx.y * E3_TILE_Y + ly;
+	const uint32_t tile = tile_order[blockIdx.x];       // longest tiles are scheduled first
+	const int tx = tile % gx, ty = tile / gx;
+	const int px = tx * E3_TILE_X + lx, py = ty * E3_TILE_Y + ly;
 	const bool inside = px < W && py < H;
 	const uint32_t pix_id = (uint32_t)W * py + px;
 	const float pixfx = (float)px, pixfy = (float)py;
-	const float tile_x0 = (float)(blockIdx.x * E3_TILE_X), tile_y0 = (float)(blockIdx.y * E3_TILE_Y);
-	const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+	const float tile_x0 = (float)(tx * E3_TILE_X), tile_y0 = (float)(ty * E3_TILE_Y);
+	const uint2 range = ranges[tile];
 	const int total = (int)(range.y - range.x);
 	bool done = !inside;
 	float T = 1.0f;
@@ -90,8 +93,8 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 			const float4* r = rec + 3 * (size_t)id;
 			const float4 a = __ldg(r);
 			const float4 e = __ldg(r + 2);     // c2, hx, hy, -
-			sA[threadIdx.x] = a;
-			sB[threadIdx.x] = __ldg(r + 1);
+			sAB[2 * threadIdx.x] = a;
+			sAB[2 * threadIdx.x + 1] = __ldg(r + 1);
 			if (C == 3) sC[threadIdx.x] = e.x;
 			sMask[threadIdx.x] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
 		}
@@ -105,8 +108,8 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 				const int j = c0 + __ffs(m) - 1;
 				m &= m - 1;
 				if (done) continue;
-				const float4 a = sA[j];
-				const float4 b = sB[j];
+				const float4 a = sAB[2 * j];
+				const float4 b = sAB[2 * j + 1];
 				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
 				const float power = eval_power(dx, dy, a.z, a.w, b.x);
 				if (power > 0.0f) continue;
@@ -167,14 +170,13 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], int lane)
 }
 
 template <int C>
-__global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges,
-	const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
+__global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+	int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
 	const float4* __restrict__ rec, const float* __restrict__ final_Ts,
 	const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
 	float* __restrict__ acc)
 {
-	__shared__ float4 sA[kBatch];
-	__shared__ float4 sB[kBatch];
+	__shared__ float4 sAB[kBatch * 2];
 	__shared__ float sC[kBatch];
 	__shared__ uint32_t sId[kBatch];
 	__shared__ uint8_t sMask[kBatch];
@@ -182,12 +184,14 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	int lx, ly;
 	pixel_of_thread(lx, ly);
 	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-	const int px = blockIdx.x * E3_TILE_X + lx, py = blockIdx.y * E3_TILE_Y + ly;
+	const uint32_t tile = tile_order[blockIdx.x];
+	const int tx = tile % gx, ty = tile / gx;
+	const int px = tx * E3_TILE_X + lx, py = ty * E3_TILE_Y + ly;
 	const bool inside = px < W && py < H;
 	const uint32_t pix_id = (uint32_t)W * py + px;
 	const float pixfx = (float)px, pixfy = (float)py;
-	const float tile_x0 = (float)(blockIdx.x * E3_TILE_X), tile_y0 = (float)(blockIdx.y * E3_TILE_Y);
-	const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+	const float tile_x0 = (float)(tx * E3_TILE_X), tile_y0 = (float)(ty * E3_TILE_Y);
+	const uint2 range = ranges[tile];
 	const float T_final = inside ? final_Ts[pix_id] : 0.f;
 	float T = T_final;
 	const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
@@ -226,8 +230,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const float4 a = __ldg(r);
 			const float4 e = __ldg(r + 2);
 			sId[threadIdx.x] = id;
-			sA[threadIdx.x] = a;
-			sB[threadIdx.x] = __ldg(r + 1);
+			sAB[2 * threadIdx.x] = a;
+			sAB[2 * threadIdx.x + 1] = __ldg(r + 1);
 			if (C == 3) sC[threadIdx.x] = e.x;
 			sMask[threadIdx.x] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
 		}
@@ -242,8 +246,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const int j = c0 + __ffs(m) - 1;
 			m &= m - 1;
 			const int contributor = total - 1 - (b0 + j);
-			const float4 a = sA[j];
-			const float4 b = sB[j];
+			const float4 a = sAB[2 * j];
+			const float4 b = sAB[2 * j + 1];
 			const float dx = a.x - pixfx, dy = a.y - pixfy;
 			const float power = eval_power(dx, dy, a.z, a.w, b.x);
 			const float G = expf(power);
@@ -301,25 +305,65 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	}
 }
 
+// Approximate longest-processing-time-first schedule: tiles are bucketed by list length (64
+// classes relative to the longest list) and emitted longest class first, so that the last wave of
+// CTAs of the blend kernels is made of short tiles instead of whatever the raster order leaves.
+__global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, int T, uint32_t* __restrict__ order)
+{
+	__shared__ uint32_t s_max, cnt[64], start[64];
+	if (threadIdx.x == 0) s_max = 0;
+	if (threadIdx.x < 64) cnt[threadIdx.x] = 0;
+	__syncthreads();
+	uint32_t m = 0;
+	for (int t = threadIdx.x; t < T; t += blockDim.x) { const uint2 r = ranges[t]; m = max(m, r.y - r.x); }
+	for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(E3_FULL, m, o));
+	if ((threadIdx.x & 31) == 0) atomicMax(&s_max, m);
+	__syncthreads();
+	const uint32_t mx = s_max + 1;
+	for (int t = threadIdx.x; t < T; t += blockDim.x) {
+		const uint2 r = ranges[t];
+		const uint32_t b = 63u - min(63u, (uint32_t)(((uint64_t)(r.y - r.x) * 64u) / mx));
+		atomicAdd(&cnt[b], 1u);
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint32_t run = 0;
+		for (int b = 0; b < 64; b++) { start[b] = run; run += cnt[b]; cnt[b] = 0; }
+	}
+	__syncthreads();
+	for (int t = threadIdx.x; t < T; t += blockDim.x) {
+		const uint2 r = ranges[t];
+		const uint32_t b = 63u - min(63u, (uint32_t)(((uint64_t)(r.y - r.x) * 64u) / mx));
+		order[start[b] + atomicAdd(&cnt[b], 1u)] = (uint32_t)t;
+	}
+}
+
 }  // namespace
 
-cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* point_list,
-	const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t st)
+cudaError_t e3_launch_tile_order(const uint2* ranges, int T, uint32_t* order, cudaStream_t st)
 {
-	const dim3 grid(f.gx, f.gy, 1);
-	if (f.C == 1) render_fwd_kernel<1><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
-	else render_fwd_kernel<3><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
+	tile_order_kernel<<<1, 1024, 0, st>>>(ranges, T, order);
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
-cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* point_list,
+cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order, const uint32_t* point_list,
+	const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t st)
+{
+	const unsigned grid = (unsigned)(f.gx * f.gy);
+	if (f.C == 1) render_fwd_kernel<1><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
+	else render_fwd_kernel<3><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
+	g_e3_launches += 1;
+	return cudaGetLastError();
+}
+
+cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order, const uint32_t* point_list,
 	const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
 	float* acc, cudaStream_t st)
 {
-	const dim3 grid(f.gx, f.gy, 1);
-	if (f.C == 1) render_bwd_kernel<1><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
-	else render_bwd_kernel<3><<<grid, 256, 0, st>>>(ranges, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
+	const unsigned grid = (unsigned)(f.gx * f.gy);
+	if (f.C == 1) render_bwd_kernel<1><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
+	else render_bwd_kernel<3><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }

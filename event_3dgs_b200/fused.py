@@ -100,10 +100,40 @@ def event_loss_and_seeds(image, image_now, image_next, gt, c, deblur=False, upst
     return out, seeds
 
 
-def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False):
+def same_view(cam_a, cam_b):
+    """True when two camera objects describe the same pose, intrinsics and image size, judged from
+    HOST-side data only (no device sync). The reference builds its train, event and blurry camera
+    lists from the same COLMAP extrinsics/intrinsics (scene/dataset_readers.py:145-160), so
+    train_cam[i] and event_cam[i] are the same view and train.py renders it twice per iteration."""
+    if cam_a is cam_b:
+        return True
+    try:
+        import numpy as np
+        if cam_a.R is None or cam_a.T is None or cam_b.R is None or cam_b.T is None:
+            return False
+        return (int(cam_a.image_width) == int(cam_b.image_width) and int(cam_a.image_height) == int(cam_b.image_height) and
+                float(cam_a.FoVx) == float(cam_b.FoVx) and float(cam_a.FoVy) == float(cam_b.FoVy) and
+                np.array_equal(np.asarray(cam_a.R), np.asarray(cam_b.R)) and
+                np.array_equal(np.asarray(cam_a.T), np.asarray(cam_b.T)) and
+                np.array_equal(np.asarray(getattr(cam_a, "trans", 0.0)), np.asarray(getattr(cam_b, "trans", 0.0))) and
+                float(getattr(cam_a, "scale", 1.0)) == float(getattr(cam_b, "scale", 1.0)))
+    except AttributeError:
+        return False
+
+
+def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
+                             dedupe_views=False):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
-    (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes."""
+    (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
+
+    dedupe_views (opt-in): when the intensity camera and the first event camera are the same view
+    (see same_view) it is rendered ONCE and its two loss seeds are summed before one backward pass;
+    loss and parameter gradients are unchanged up to fp32 summation order. The screen-space
+    gradient handed to the densification statistics then contains both loss terms of that view
+    (the reference's contains only the intensity term), which is why this is not the default."""
+    if dedupe_views and same_view(cam_train, cam_now):
+        return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg)
     for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg,
               gt["event_now"], gt["event_next"], gt["intensity"]):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
@@ -134,6 +164,34 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
                "radii": sts[0].radii, "num_rendered": [s.R for s in sts], "loss_terms": out}
         return loss, pkg
     return loss
+
+
+def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg):
+    st_a = _forward_raw(pc, cam_a, bg)
+    st_n = _forward_raw(pc, cam_next, bg)
+    out, seeds = event_loss_and_seeds(st_a.color, st_a.color, st_n.color, gt, c, deblur)
+    seeds["image"].add_(seeds["image_now"])
+    D = int(pc.active_sh_degree)
+    grads = {"xyz": torch.empty_like(pc._xyz), "features_dc": torch.empty_like(pc._features_dc),
+             "opacity": torch.empty_like(pc._opacity), "scaling": torch.empty_like(pc._scaling),
+             "rotation": torch.empty_like(pc._rotation),
+             "features_rest": torch.empty_like(pc._features_rest) if D > 0 else _zeros_like_cached(pc._features_rest)}
+    d_mean2D = torch.empty_like(pc._xyz)
+    _backward_raw(pc, st_a, bg, seeds["image"], grads, False, d_mean2D)
+    _backward_raw(pc, st_n, bg, seeds["image_next"], grads, True)
+    pc._xyz.grad = grads["xyz"]
+    pc._features_dc.grad = grads["features_dc"]
+    pc._features_rest.grad = grads["features_rest"]
+    pc._opacity.grad = grads["opacity"]
+    pc._scaling.grad = grads["scaling"]
+    pc._rotation.grad = grads["rotation"]
+    c.grad = out[1].reshape(c.shape).clone()
+    if return_pkg:
+        vsp = torch.zeros_like(pc._xyz)
+        vsp.grad = d_mean2D
+        return out[0], {"render": st_a.color, "viewspace_points": vsp, "visibility_filter": st_a.radii > 0,
+                        "radii": st_a.radii, "num_rendered": [st_a.R, st_n.R], "loss_terms": out}
+    return out[0]
 
 
 _ZERO_CACHE = {}

@@ -89,7 +89,7 @@ class GaussianParams(nn.Module):
 def make_camera(cam, device, image=None):
     """numpy camera dict of synthetic.make_camera -> the attributes render() reads (scene/cameras.py)."""
     t = lambda a: torch.as_tensor(a, dtype=torch.float32).to(device)
-    return SimpleNamespace(FoVx=cam["FoVx"], FoVy=cam["FoVy"], image_width=cam["image_width"],
+    return SimpleNamespace(R=cam.get("R"), T=cam.get("T"), FoVx=cam["FoVx"], FoVy=cam["FoVy"], image_width=cam["image_width"],
                            image_height=cam["image_height"], world_view_transform=t(cam["world_view_transform"]),
                            full_proj_transform=t(cam["full_proj_transform"]), camera_center=t(cam["camera_center"]),
                            original_image=None if image is None else t(image))

@@ -60,7 +60,8 @@ def make_camera(i, n_views, W, H, fovx_deg=60.0, radius=4.0, height=0.6):
     wvt = np.ascontiguousarray(V.T)                               # transposed storage
     full = np.ascontiguousarray((wvt @ Pm.T).astype(np.float32))  # cameras.py:56
     center = np.linalg.inv(wvt.astype(np.float64))[3, :3].astype(np.float32)
-    return dict(world_view_transform=wvt, full_proj_transform=full, camera_center=center,
+    # R, T in the reference's Camera convention (scene/cameras.py: R = camera-to-world rotation, T = w2c translation)
+    return dict(R=np.ascontiguousarray(Rwc.T), T=(-Rwc @ c).copy(), world_view_transform=wvt, full_proj_transform=full, camera_center=center,
                 FoVx=fovx, FoVy=fovy, tanfovx=math.tan(fovx * 0.5), tanfovy=math.tan(fovy * 0.5),
                 image_width=W, image_height=H)
 

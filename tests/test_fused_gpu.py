@@ -127,3 +127,21 @@ def test_dist2_matches_bruteforce_oracle(cuda_dev):
     D[np.arange(200), idx] = np.inf
     ref = np.sort(np.partition(D, 3, axis=1)[:, :3], 1).mean(1)
     assert np.allclose(got[idx], ref, rtol=1e-4)
+
+
+def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev):
+    from event_3dgs_b200 import fused
+    pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, 0, True)
+    leaves = pc.leaves() + [c]
+    assert fused.same_view(cams[3], cams[3]) and not fused.same_view(cams[3], cams[4])
+    la = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True)
+    ga = [p.grad.clone() for p in leaves]
+    lb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
+    gb = [p.grad.clone() for p in leaves]
+    assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
+    for a, b in zip(ga, gb):
+        assert rel_err(b.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    # different views: the flag changes nothing
+    lc = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
+    ld = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True)
+    assert abs(lc.item() - ld.item()) <= 1e-6 * abs(ld.item())
