@@ -27,11 +27,11 @@ SIGNATURES = {
     "e3_rasterize_backward": (_i, [_i, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp,
                                    _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp, _vp, _vp, _vp, _i, _vp]),
-    "e3_rasterize_forward_raw": (_i, [ALLOC_FN, _vp, ALLOC_FN, _vp, ALLOC_FN, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp,
+    "e3_rasterize_forward_raw": (_i, [ALLOC_FN, _vp, ALLOC_FN, _vp, ALLOC_FN, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp,
                                       _vp, _f, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp, ctypes.POINTER(_i)]),
-    "e3_rasterize_backward_raw": (_i, [_i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
+    "e3_rasterize_backward_raw": (_i, [_i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
                                        _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
-    "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
+    "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "e3_dist2_scratch_bytes": (_sz, [_i]),
     "e3_dist2": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
@@ -46,6 +46,16 @@ SIGNATURES = {
     "e3_binning_ptr": (_vp, [_vp, _i, _i]),
     "e3_image_ptr": (_vp, [_vp, _i, _i, _i]),
 }
+
+
+
+class AdamGroup(ctypes.Structure):
+    """e3_adam_group of include/event3dgs.h."""
+    _fields_ = [("param", ctypes.c_void_p), ("grad", ctypes.c_void_p), ("exp_avg", ctypes.c_void_p),
+                ("exp_avg_sq", ctypes.c_void_p), ("n", ctypes.c_ulonglong), ("lr", ctypes.c_float), ("eps", ctypes.c_float)]
+
+
+SIGNATURES["e3_adam_step"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, _vp])
 
 _lib = None
 

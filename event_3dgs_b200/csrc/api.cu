@@ -135,7 +135,7 @@ static int forward_impl(
 		!viewmatrix || !projmatrix || !out_color || !radii || !num_rendered_host)
 		return E3_ERR_BAD_ARGUMENT;
 	if (!colors_precomp && (!shs || !cam_pos)) return E3_ERR_BAD_ARGUMENT;
-	if (!colors_precomp && channels != 3) return E3_ERR_UNSUPPORTED;
+	if (!colors_precomp && channels != 3 && !raw) return E3_ERR_UNSUPPORTED;
 	if (!cov3D_precomp && (!scales || !rotations)) return E3_ERR_BAD_ARGUMENT;
 
 	E3Frame f = make_frame(P, D, M, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
@@ -150,7 +150,7 @@ static int forward_impl(
 
 	E3_CHECK(cudaMemsetAsync(g.flags, 0, 4 * sizeof(int), st));
 	E3_STAGE(E3_STAGE_PREPROCESS_FWD, e3_launch_preprocess(f, means3D, scales, rotations, opacities, shs, f_rest, raw, cov3D_precomp, colors_precomp,
-		viewmatrix, projmatrix, cam_pos, prefiltered != 0, radii, g, st));
+		viewmatrix, projmatrix, cam_pos, prefiltered != 0, radii, g, background, st));
 
 	// depth order of the Gaussians (culled ones carry key 0xffffffff and emit nothing)
 	int dres = 0;
@@ -180,7 +180,9 @@ static int forward_impl(
 	if (bres != 0) return E3_ERR_BAD_ARGUMENT;
 	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
 	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_order(im.ranges, (int)T, im.tile_order, st));
-	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib, out_color, st));
+	// single-channel raw mode blends against the luma of the background (written by the preprocess kernel)
+	const float* bg_used = (raw && channels == 1) ? reinterpret_cast<const float*>(g.flags) + 2 : background;
+	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib, out_color, st));
 	return 0;
 }
 
@@ -206,7 +208,7 @@ int e3_rasterize_forward_raw(
 	e3_alloc_fn geometry_alloc, void* geometry_ctx,
 	e3_alloc_fn binning_alloc, void* binning_ctx,
 	e3_alloc_fn image_alloc, void* image_ctx,
-	int P, int active_sh_degree,
+	int P, int active_sh_degree, int channels,
 	const float* background, int width, int height,
 	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
 	const float* log_scales, float scale_modifier, const float* raw_rotations,
@@ -214,9 +216,9 @@ int e3_rasterize_forward_raw(
 	float tan_fovx, float tan_fovy,
 	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host)
 {
-	if (active_sh_degree < 0 || active_sh_degree > 3) return E3_ERR_BAD_ARGUMENT;
+	if (active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
 	if (P > 0 && (!features_dc || (active_sh_degree > 0 && !features_rest))) return E3_ERR_BAD_ARGUMENT;
-	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, active_sh_degree, 16, 3,
+	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, active_sh_degree, 16, channels,
 		background, width, height, xyz, features_dc, features_rest, true, nullptr, opacity_logits, log_scales, scale_modifier,
 		raw_rotations, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, 0, out_color, radii, debug, stream,
 		num_rendered_host);
@@ -260,7 +262,7 @@ int e3_rasterize_backward(
 }
 
 int e3_rasterize_backward_raw(
-	int P, int active_sh_degree, int R,
+	int P, int active_sh_degree, int channels, int R,
 	const float* background, int width, int height,
 	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
 	const float* log_scales, float scale_modifier, const float* raw_rotations,
@@ -273,20 +275,21 @@ int e3_rasterize_backward_raw(
 	int debug, void* stream)
 {
 	cudaStream_t st = (cudaStream_t)stream;
-	if (P < 0 || active_sh_degree < 0 || active_sh_degree > 3) return E3_ERR_BAD_ARGUMENT;
+	if (P < 0 || active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
 	if (P == 0) return 0;
 	if (!geometry_buffer || !image_buffer || (R > 0 && !binning_buffer) || !radii || !xyz || !features_dc || !opacity_logits ||
 		!log_scales || !raw_rotations || !dL_dpix || !d_xyz || !d_features_dc || !d_opacity_logits || !d_log_scales ||
 		!d_raw_rotations || !viewmatrix || !projmatrix || !campos)
 		return E3_ERR_BAD_ARGUMENT;
 	if (active_sh_degree > 0 && (!features_rest || !d_features_rest)) return E3_ERR_BAD_ARGUMENT;
-	E3Frame f = make_frame(P, active_sh_degree, 16, 3, width, height, tan_fovx, tan_fovy, scale_modifier);
+	E3Frame f = make_frame(P, active_sh_degree, 16, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
 	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
 	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
+	const float* bg_used = channels == 1 ? reinterpret_cast<const float*>(g.flags) + 2 : background;
 	if (R > 0) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
-		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib,
+		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
 	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,
@@ -297,17 +300,17 @@ int e3_rasterize_backward_raw(
 
 int e3_event_loss(int width, int height, const float* image, const float* image_now, const float* image_next,
 	const float* gt_now, const float* gt_next, const float* gt_intensity, const float* gt_blur, const float* c,
-	float upstream, void* scratch, size_t scratch_bytes, float* d_image, float* d_image_now, float* d_image_next,
-	float* out5, void* stream)
+	float upstream, int event_channels, void* scratch, size_t scratch_bytes, float* d_image, float* d_image_now,
+	float* d_image_next, float* out5, void* stream)
 {
 	cudaStream_t st = (cudaStream_t)stream;
 	const int debug = 0;
-	if (width <= 0 || height <= 0 || !image || !image_now || !image_next || !gt_now || !gt_next || !gt_intensity || !c ||
+	if ((event_channels != 1 && event_channels != 3) || width <= 0 || height <= 0 || !image || !image_now || !image_next || !gt_now || !gt_next || !gt_intensity || !c ||
 		!scratch || scratch_bytes < 8 * sizeof(double) || (reinterpret_cast<size_t>(scratch) & 7) || !d_image || !d_image_now ||
 		!d_image_next || !out5)
 		return E3_ERR_BAD_ARGUMENT;
 	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_loss((size_t)width * height, image, image_now, image_next, gt_now, gt_next,
-		gt_intensity, gt_blur, c, upstream, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
+		gt_intensity, gt_blur, c, upstream, event_channels, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
 	return 0;
 }
 

@@ -52,7 +52,7 @@ struct E3GeomState {
 	uint32_t* sort_counts;    // [e3_sort_scratch_words(P)]
 	uint32_t* scan_tmp;       // [scan_blocks(P) + 2]
 	float* acc;               // [P * E3_ACC_STRIDE] backward accumulators
-	int* flags;               // [4]: 0 num_rendered, 1 prefiltered-violation
+	int* flags;               // [4]: 0 num_rendered, 1 prefiltered-violation, 2 (as float) luma of the background
 	static E3GeomState carve(char* p, size_t P, char** end = nullptr)
 	{
 		E3GeomState s;
@@ -125,7 +125,7 @@ struct E3Frame {
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
 	const float* rotations, const float* opacities, const float* shs, const float* f_rest, bool raw,
 	const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
-	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st);
+	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, const float* bg3, cudaStream_t st);
 cudaError_t e3_launch_mark_visible(int P, const float* means3D, const float* viewmatrix,
 	uint8_t* present, cudaStream_t st);
 cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D,
@@ -137,7 +137,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	float* dL_dscale, float* dL_drot, cudaStream_t st);
 cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
 	const float* gt_now, const float* gt_next, const float* gt_int, const float* gt_blur, const float* c_ptr,
-	float upstream, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st);
+	float upstream, int event_channels, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st);
 
 // out[i] = sum_{j<i} in[idx ? idx[j] : j]; total (optional, device) = sum of all
 cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint32_t* out,

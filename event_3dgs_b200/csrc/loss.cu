@@ -20,6 +20,14 @@ namespace {
 #define LUMA_B 0.1804f
 #define EVT_EPS 1e-8f
 
+// EC = channels of the two event renders: 3 (RGB, luma taken here) or 1 (already luma)
+template <int EC>
+__device__ __forceinline__ float luma_ev(const float* __restrict__ img, size_t i, size_t N)
+{
+	if (EC == 1) return __ldg(img + i);
+	return LUMA_R * __ldg(img + i) + LUMA_G * __ldg(img + N + i) + LUMA_B * __ldg(img + 2 * N + i);
+}
+
 __device__ __forceinline__ float luma3(const float* __restrict__ img, size_t i, size_t N)
 {
 	// utils/loss_utils.py:25, evaluated left to right like the PyTorch expression
@@ -43,6 +51,7 @@ __device__ __forceinline__ double block_sum(double v, double* sm)
 
 // sums[0] = sum |d - g|, [1] = #(g != 0), [2] = sum |image - gt_int| (3N terms),
 // [3] = sum |image - gt_blur|, [4] = sum sgn(d - g) * d
+template <int EC>
 __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const float* __restrict__ image,
 	const float* __restrict__ image_now, const float* __restrict__ image_next, const float* __restrict__ gt_now,
 	const float* __restrict__ gt_next, const float* __restrict__ gt_int, const float* __restrict__ gt_blur,
@@ -52,7 +61,7 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 	const float c = __ldg(c_ptr);
 	double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0;
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
-		const float y1 = luma3(image_now, i, N), y2 = luma3(image_next, i, N);
+		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
 		const float g = (logf(luma3(gt_next, i, N) + EVT_EPS) - logf(luma3(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		s0 += fabsf(d - g);
@@ -75,6 +84,7 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 
 // out[0] = loss, out[1] = dL/dc, out[2] = loss1 (event L1), out[3] = loss2 (intensity L1),
 // out[4] = fraction of pixels with a non-zero GT event difference
+template <int EC>
 __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const float* __restrict__ image,
 	const float* __restrict__ image_now, const float* __restrict__ image_next, const float* __restrict__ gt_now,
 	const float* __restrict__ gt_next, const float* __restrict__ gt_int, const float* __restrict__ gt_blur,
@@ -97,14 +107,17 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 		out[2] = (float)loss1; out[3] = (float)loss2; out[4] = (float)f;
 	}
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
-		const float y1 = luma3(image_now, i, N), y2 = luma3(image_next, i, N);
+		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
 		const float g = (logf(luma3(gt_next, i, N) + EVT_EPS) - logf(luma3(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		const float s = sgn(d - g);
 		const float dy2 = k1 * s / (c * (y2 + EVT_EPS));
 		const float dy1 = -k1 * s / (c * (y1 + EVT_EPS));
-		d_now[i] = LUMA_R * dy1; d_now[N + i] = LUMA_G * dy1; d_now[2 * N + i] = LUMA_B * dy1;
-		d_next[i] = LUMA_R * dy2; d_next[N + i] = LUMA_G * dy2; d_next[2 * N + i] = LUMA_B * dy2;
+		if (EC == 1) { d_now[i] = dy1; d_next[i] = dy2; }
+		else {
+			d_now[i] = LUMA_R * dy1; d_now[N + i] = LUMA_G * dy1; d_now[2 * N + i] = LUMA_B * dy1;
+			d_next[i] = LUMA_R * dy2; d_next[N + i] = LUMA_G * dy2; d_next[2 * N + i] = LUMA_B * dy2;
+		}
 #pragma unroll
 		for (int ch = 0; ch < 3; ch++) {
 			const float v = __ldg(image + ch * N + i);
@@ -119,14 +132,20 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 
 cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
 	const float* gt_now, const float* gt_next, const float* gt_int, const float* gt_blur, const float* c_ptr,
-	float upstream, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st)
+	float upstream, int event_channels, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st)
 {
 	cudaError_t e = cudaMemsetAsync(sums, 0, 8 * sizeof(double), st);
 	if (e != cudaSuccess) return e;
 	const int grid = (int)min((size_t)148 * 8, (N + 255) / 256);
-	event_loss_reduce_kernel<<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums);
-	event_loss_seed_kernel<<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums,
-		upstream, d_image, d_now, d_next, out);
+	if (event_channels == 1) {
+		event_loss_reduce_kernel<1><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums);
+		event_loss_seed_kernel<1><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums,
+			upstream, d_image, d_now, d_next, out);
+	} else {
+		event_loss_reduce_kernel<3><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums);
+		event_loss_seed_kernel<3><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums,
+			upstream, d_image, d_now, d_next, out);
+	}
 	g_e3_launches += 2;
 	return cudaGetLastError();
 }

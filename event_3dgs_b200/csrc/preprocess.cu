@@ -108,6 +108,9 @@ __constant__ float kSH_C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31
 	-1.0925484305920792f, 0.5462742152960396f };
 __constant__ float kSH_C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
 	0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
+#define E3_LUMA_R 0.4124f
+#define E3_LUMA_G 0.35758f
+#define E3_LUMA_B 0.1804f
 #define SH_C0 0.28209479177387814f
 #define SH_C1 0.4886025119029199f
 
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 	bool prefiltered, int* __restrict__ radii, float* __restrict__ depths, float4* __restrict__ rec,
 	float* __restrict__ cov3Ds, float* __restrict__ rgb, uint8_t* __restrict__ clamped,
 	uint32_t* __restrict__ tiles_touched, uint2* __restrict__ rect, uint32_t* __restrict__ dkey,
-	uint32_t* __restrict__ dval, float* __restrict__ acc, int* __restrict__ flags)
+	uint32_t* __restrict__ dval, float* __restrict__ acc, int* __restrict__ flags, const float* __restrict__ bg3)
 {
 	__shared__ float s_xyz[256 * 3];
 	__shared__ float s_scl[256 * 3];
@@ -209,6 +212,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 	const size_t idx = first + t;
 	const float* vm = s_m;
 	const float* pm = s_m + 16;
+	if (RAW && C == 1 && idx == 0)      // luma of the 3-channel background, kept with the state for both blend passes
+		reinterpret_cast<float*>(flags)[2] = E3_LUMA_R * bg3[0] + E3_LUMA_G * bg3[1] + E3_LUMA_B * bg3[2];
 	if (RAW) {    // scaling_activation = exp (gaussian_model.py:28)
 		s_scl[3 * t] = expf(s_scl[3 * t]); s_scl[3 * t + 1] = expf(s_scl[3 * t + 1]); s_scl[3 * t + 2] = expf(s_scl[3 * t + 2]);
 	}
@@ -270,6 +275,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 			col[0] = v.x; col[1] = v.y; col[2] = v.z;
 			rgb[idx * 3] = v.x; rgb[idx * 3 + 1] = v.y; rgb[idx * 3 + 2] = v.z;
 			clamped[idx * 3] = cl[0]; clamped[idx * 3 + 1] = cl[1]; clamped[idx * 3 + 2] = cl[2];
+			// single-channel mode of the raw path: blend the luma of utils/loss_utils.py:25 directly
+			// (blending is linear in colour, so this equals the luma of the RGB render)
+			if (RAW && C == 1) col[0] = E3_LUMA_R * v.x + E3_LUMA_G * v.y + E3_LUMA_B * v.z;
 		}
 		my_radius = rad;
 		tt = (y1 - y0) * (x1 - x0);
@@ -487,7 +495,9 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	if (RAW) { fdc[0] = s_fdc[3 * t]; fdc[1] = s_fdc[3 * t + 1]; fdc[2] = s_fdc[3 * t + 2]; }
 	__syncthreads();          // every staged input row is in registers: the buffers now carry outputs
 
-	const float dcol[3] = { a1.z, a1.w, a2.x };
+	// single-channel raw mode: the blend produced dL/dY; dL/dcolour_k = w_k dL/dY
+	const float dcol[3] = { (RAW && C == 1) ? E3_LUMA_R * a1.z : a1.z, (RAW && C == 1) ? E3_LUMA_G * a1.z : a1.w,
+		(RAW && C == 1) ? E3_LUMA_B * a1.z : a2.x };
 	if (live) {
 		if (dL_dconic) reinterpret_cast<float4*>(dL_dconic)[idx] = make_float4(a0.z, a0.w, 0.f, a1.x);
 		if (!RAW) {
@@ -671,7 +681,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
 	const float* rotations, const float* opacities, const float* shs, const float* f_rest, bool raw,
 	const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
-	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, cudaStream_t st)
+	const float* cam_pos, bool prefiltered, int* radii, E3GeomState& g, const float* bg3, cudaStream_t st)
 {
 	const int grid = (f.P + 255) / 256;
 	const size_t dyn = (raw && f.D > 0) ? (size_t)256 * 45 * sizeof(float) : 0;
@@ -680,14 +690,17 @@ cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const f
 		if (!attr_set) {
 			cudaError_t ea = cudaFuncSetAttribute(preprocess_fwd_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
 			if (ea != cudaSuccess) return ea;
+			ea = cudaFuncSetAttribute(preprocess_fwd_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+			if (ea != cudaSuccess) return ea;
 			attr_set = true;
 		}
 	}
 #define LAUNCH(CH, RW) preprocess_fwd_kernel<CH, RW><<<grid, 256, dyn, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
 	rotations, opacities, shs, f_rest, cov3D_precomp, colors_precomp, viewmatrix, projmatrix, cam_pos, f.W, f.H, \
 	f.tan_fovx, f.tan_fovy, f.focal_x, f.focal_y, f.gx, f.gy, prefiltered, radii, g.depths, g.rec, g.cov3D, g.rgb, \
-	g.clamped, g.tiles_touched, g.rect, g.dkey[0], g.dval[0], g.acc, g.flags)
-	if (raw) LAUNCH(3, true); else if (f.C == 1) LAUNCH(1, false); else LAUNCH(3, false);
+	g.clamped, g.tiles_touched, g.rect, g.dkey[0], g.dval[0], g.acc, g.flags, bg3)
+	if (raw) { if (f.C == 1) LAUNCH(1, true); else LAUNCH(3, true); }
+	else if (f.C == 1) LAUNCH(1, false); else LAUNCH(3, false);
 #undef LAUNCH
 	g_e3_launches += 1;
 	return cudaGetLastError();
@@ -723,7 +736,10 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
 	dL_dscale, dL_drot); } while (0)
-	if (raw) {
+	if (raw && f.C == 1) {
+		if (shrest) { if (accumulate) LAUNCH(1, true, true, true); else LAUNCH(1, true, false, true); }
+		else { if (accumulate) LAUNCH(1, true, true, false); else LAUNCH(1, true, false, false); }
+	} else if (raw) {
 		if (shrest) { if (accumulate) LAUNCH(3, true, true, true); else LAUNCH(3, true, false, true); }
 		else { if (accumulate) LAUNCH(3, true, true, false); else LAUNCH(3, true, false, false); }
 	}

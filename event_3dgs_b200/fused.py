@@ -21,10 +21,10 @@ from .rasterizer import _ALLOC_CB, _slots
 
 
 class RenderState:
-    __slots__ = ("R", "color", "radii", "geom", "binning", "img", "cam", "tanfovx", "tanfovy")
+    __slots__ = ("R", "color", "radii", "geom", "binning", "img", "cam", "tanfovx", "tanfovy", "channels")
 
 
-def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False):
+def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False, channels=3):
     L = _lib.lib()
     xyz = pc._xyz
     P = xyz.shape[0]
@@ -35,18 +35,19 @@ def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False):
     st.tanfovx = math.tan(cam.FoVx * 0.5)
     st.tanfovy = math.tan(cam.FoVy * 0.5)
     st.radii = torch.empty(P, dtype=torch.int32, device=dev)
+    st.channels = channels
     empty = torch.empty(0, dtype=torch.uint8, device=dev)
     if P == 0:
-        st.R, st.color, st.geom, st.binning, st.img = 0, torch.zeros(3, H, W, device=dev), empty, empty, empty
+        st.R, st.color, st.geom, st.binning, st.img = 0, torch.zeros(channels, H, W, device=dev), empty, empty, empty
         return st
-    st.color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+    st.color = torch.empty(channels, H, W, dtype=torch.float32, device=dev)
     D = int(pc.active_sh_degree)
     R = ctypes.c_int(0)
     _slots.clear()
     _slots["device"] = dev
     with torch.cuda.device(dev):
         code = L.e3_rasterize_forward_raw(
-            _ALLOC_CB, 1, _ALLOC_CB, 2, _ALLOC_CB, 3, P, D, bg.data_ptr(), W, H, xyz.data_ptr(), pc._features_dc.data_ptr(),
+            _ALLOC_CB, 1, _ALLOC_CB, 2, _ALLOC_CB, 3, P, D, channels, bg.data_ptr(), W, H, xyz.data_ptr(), pc._features_dc.data_ptr(),
             pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(), float(scaling_modifier),
             pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(), cam.full_proj_transform.data_ptr(),
             cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.color.data_ptr(), st.radii.data_ptr(), int(debug),
@@ -69,7 +70,7 @@ def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling
     D = int(pc.active_sh_degree)
     with torch.cuda.device(dev):
         code = L.e3_rasterize_backward_raw(
-            P, D, st.R, bg.data_ptr(), int(cam.image_width), int(cam.image_height), xyz.data_ptr(),
+            P, D, st.channels, st.R, bg.data_ptr(), int(cam.image_width), int(cam.image_height), xyz.data_ptr(),
             pc._features_dc.data_ptr(), pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(),
             float(scaling_modifier), pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(),
             cam.full_proj_transform.data_ptr(), cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.radii.data_ptr(),
@@ -82,18 +83,22 @@ def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling
 
 
 def event_loss_and_seeds(image, image_now, image_next, gt, c, deblur=False, upstream=1.0):
-    """e3_event_loss: returns (out5 tensor [loss, dL/dc, loss1, loss2, f], seeds dict)."""
+    """e3_event_loss: returns (out5 tensor [loss, dL/dc, loss1, loss2, f], seeds dict). image_now and
+    image_next are both [3,H,W] or both [1,H,W] (luma renders)."""
     L = _lib.lib()
     dev = image.device
     _, H, W = image.shape
-    seeds = {k: torch.empty_like(image) for k in ("image", "image_now", "image_next")}
+    ec = int(image_now.shape[0])
+    if ec != int(image_next.shape[0]) or ec not in (1, 3):
+        raise RuntimeError("event_loss_and_seeds: the two event renders must both have 1 or both have 3 channels")
+    seeds = {"image": torch.empty_like(image), "image_now": torch.empty_like(image_now), "image_next": torch.empty_like(image_next)}
     out = torch.empty(5, dtype=torch.float32, device=dev)
     scratch = torch.empty(8, dtype=torch.float64, device=dev)
     blur = gt["blurry"] if deblur else None
     with torch.cuda.device(dev):
         code = L.e3_event_loss(W, H, image.data_ptr(), image_now.data_ptr(), image_next.data_ptr(),
                                gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr(),
-                               None if blur is None else blur.data_ptr(), c.data_ptr(), float(upstream), scratch.data_ptr(), 64,
+                               None if blur is None else blur.data_ptr(), c.data_ptr(), float(upstream), ec, scratch.data_ptr(), 64,
                                seeds["image"].data_ptr(), seeds["image_now"].data_ptr(), seeds["image_next"].data_ptr(),
                                out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
     _lib.check(code)
@@ -122,7 +127,7 @@ def same_view(cam_a, cam_b):
 
 
 def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
-                             dedupe_views=False):
+                             dedupe_views=False, gray_event_views=True):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
@@ -131,14 +136,20 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     (see same_view) it is rendered ONCE and its two loss seeds are summed before one backward pass;
     loss and parameter gradients are unchanged up to fp32 summation order. The screen-space
     gradient handed to the densification statistics then contains both loss terms of that view
-    (the reference's contains only the intensity term), which is why this is not the default."""
+    (the reference's contains only the intensity term), which is why this is not the default.
+
+    gray_event_views: render the two event views with one channel, the luma that
+    differentialable_event_simu takes of them anyway (utils/loss_utils.py:24-28,240-241); the
+    algebraic rewrite behind the reference's --gray idea. Equal to the
+    3-channel route up to fp32 rounding; False reproduces the 3-channel renders exactly."""
     if dedupe_views and same_view(cam_train, cam_now):
         return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg)
     for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg,
               gt["event_now"], gt["event_next"], gt["intensity"]):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("event_3dgs_b200.fused: tensors must be contiguous float32 CUDA tensors")
-    sts = [_forward_raw(pc, cam, bg) for cam in (cam_train, cam_now, cam_next)]
+    ec = 1 if gray_event_views else 3
+    sts = [_forward_raw(pc, cam_train, bg), _forward_raw(pc, cam_now, bg, channels=ec), _forward_raw(pc, cam_next, bg, channels=ec)]
     out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
     D = int(pc.active_sh_degree)
     grads = {"xyz": torch.empty_like(pc._xyz), "features_dc": torch.empty_like(pc._features_dc),

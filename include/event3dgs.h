@@ -133,12 +133,16 @@ E3_API int e3_rasterize_backward(
  * (scene/gaussian_model.py:95-115), torch.cat of the SH features (:109-113), the view direction and
  * eval_sh + clamp_min(x + 0.5, 0) (gaussian_renderer/__init__.py:74-81, utils/sh_utils.py:57-112),
  * followed by the rasterizer call. active_sh_degree in 0..3; features_rest may be NULL at degree 0.
- * Always 3 channels. State buffers are interchangeable with e3_rasterize_forward's. */
+ * channels = 3: RGB image [3,H,W]. channels = 1: the "--gray" rewrite for views that the loss only
+ * consumes through rgb_to_LUVscale (utils/loss_utils.py:24-28): every Gaussian's clamped colour is
+ * projected to Y = 0.4124 R + 0.35758 G + 0.1804 B before blending and the image is [1,H,W]; since
+ * blending is linear in colour this equals the luma of the 3-channel render up to fp32 rounding.
+ * `background` always points to 3 floats. */
 E3_API int e3_rasterize_forward_raw(
 	e3_alloc_fn geometry_alloc, void* geometry_ctx,
 	e3_alloc_fn binning_alloc, void* binning_ctx,
 	e3_alloc_fn image_alloc, void* image_ctx,
-	int P, int active_sh_degree,
+	int P, int active_sh_degree, int channels,
 	const float* background, int width, int height,
 	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
 	const float* log_scales, float scale_modifier, const float* raw_rotations,
@@ -154,7 +158,7 @@ E3_API int e3_rasterize_forward_raw(
  * NULL at degree 0 (it is identically zero). d_mean2D [P,3] is optional: the gradient of the
  * screen-space means that train.py:319-320 feeds to the densification statistics. */
 E3_API int e3_rasterize_backward_raw(
-	int P, int active_sh_degree, int R,
+	int P, int active_sh_degree, int channels, int R,
 	const float* background, int width, int height,
 	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
 	const float* log_scales, float scale_modifier, const float* raw_rotations,
@@ -171,13 +175,35 @@ E3_API int e3_rasterize_backward_raw(
  * (image = intensity view, image_now / image_next = event views index / index+1), the GT event
  * frames, the GT intensity frame and, for --deblur, the blurry frame (else NULL). `c` points to the
  * learnable event threshold on the device (train.py:71,165); the GT threshold is the constant 0.17
- * (train.py:170). `upstream` scales all gradients (1 for loss.backward()). scratch: >= 64 bytes,
+ * (train.py:170). `upstream` scales all gradients (1 for loss.backward()). event_channels = 3:
+ * image_now / image_next and their seeds are [3,H,W]; 1: they are single-channel luma renders
+ * (channels = 1 of e3_rasterize_forward_raw) and the seeds are [1,H,W]. scratch: >= 64 bytes,
  * 8-byte aligned device memory. Outputs: the three seeds dL/dimage* [3,H,W] and
  * out5 = { loss, dL/dc, event L1, intensity L1, fraction of pixels with non-zero GT event }. */
 E3_API int e3_event_loss(int width, int height, const float* image, const float* image_now,
 	const float* image_next, const float* gt_now, const float* gt_next, const float* gt_intensity,
-	const float* gt_blur, const float* c, float upstream, void* scratch, size_t scratch_bytes,
-	float* d_image, float* d_image_now, float* d_image_next, float* out5, void* stream);
+	const float* gt_blur, const float* c, float upstream, int event_channels, void* scratch,
+	size_t scratch_bytes, float* d_image, float* d_image_now, float* d_image_next, float* out5,
+	void* stream);
+
+/* One Adam step over up to E3_ADAM_MAX_GROUPS parameter groups in a single kernel launch.
+ * Replaces gaussians.optimizer.step() (train.py:330-332) on the optimizer that
+ * scene/gaussian_model.py:149-175 builds as torch.optim.Adam(l, lr=0.0, eps=1e-15) with one group
+ * per leaf tensor, and optimizer_c.step() (train.py:71-73,212). Same arithmetic as torch (no
+ * amsgrad, no weight decay): `step` is the 1-based step count t used for the bias corrections.
+ * groups_host is an array in HOST memory; the pointers inside are device pointers to n floats. */
+#define E3_ADAM_MAX_GROUPS 8
+typedef struct e3_adam_group {
+	float* param;
+	const float* grad;
+	float* exp_avg;
+	float* exp_avg_sq;
+	unsigned long long n;
+	float lr;
+	float eps;
+} e3_adam_group;
+E3_API int e3_adam_step(const e3_adam_group* groups_host, int num_groups, int step, double beta1,
+	double beta2, void* stream);
 
 /* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
  * rasterizer_impl.cu:54-66,141-153): present[i] = view-space z > 0.2. present is uint8[P]. */

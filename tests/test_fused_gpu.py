@@ -35,7 +35,8 @@ def test_fused_iteration_matches_dropin_autograd(cuda_dev, sh_degree, deblur):
     vs_a = pkg_a["viewspace_points"].grad.clone()
     for p in leaves:
         p.grad = None
-    loss_b, pkg_b = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=deblur, return_pkg=True)
+    loss_b, pkg_b = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=deblur, return_pkg=True,
+                                                   gray_event_views=(sh_degree % 2 == 0))
     gb = [p.grad.clone() for p in leaves]
     assert abs(loss_a.item() - loss_b.item()) <= 1e-5 * abs(loss_a.item())
     # activations are evaluated by different code (ATen vs in-kernel): allow a few borderline radii
@@ -145,3 +146,30 @@ def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev):
     lc = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
     ld = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True)
     assert abs(lc.item() - ld.item()) <= 1e-6 * abs(ld.item())
+
+
+def test_fused_adam_matches_torch_adam(cuda_dev):
+    """e3_adam_step against torch.optim.Adam with the reference's six groups (gaussian_model.py:149-175)."""
+    from event_3dgs_b200.optim import FusedAdam
+    torch.manual_seed(0)
+    P = 10_007
+    shapes = [(P, 3), (P, 1, 3), (P, 15, 3), (P, 1), (P, 3), (P, 4), ()]
+    lrs = [1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3, 0.1]
+    a = [torch.randn(s, device=cuda_dev).requires_grad_() for s in shapes]
+    b = [x.detach().clone().requires_grad_() for x in a]
+    mk = lambda ps: [{"params": [p], "lr": lr, "name": str(i)} for i, (p, lr) in enumerate(zip(ps, lrs))]
+    oa = torch.optim.Adam(mk(a), lr=0.0, eps=1e-15)
+    ob = FusedAdam(mk(b), lr=0.0, eps=1e-15)
+    for it in range(5):
+        for x, y in zip(a, b):
+            g = torch.randn_like(x) * (10.0 ** (it - 3))
+            x.grad, y.grad = g.clone(), g.clone()
+        if it == 2:      # the reference reschedules the xyz learning rate every iteration (train.py:97)
+            oa.param_groups[0]["lr"] = ob.param_groups[0]["lr"] = 8e-5
+        oa.step()
+        ob.step()
+    for x, y in zip(a, b):
+        assert rel_err(y.detach().cpu().numpy(), x.detach().cpu().numpy()) < 1e-6
+    for x, y in zip(a, b):
+        assert rel_err(ob.state[y]["exp_avg_sq"].cpu().numpy(), oa.state[x]["exp_avg_sq"].cpu().numpy()) < 2e-6
+        assert int(ob.state[y]["step"]) == 5
