@@ -194,13 +194,22 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	const uint32_t gb = block_excl_scan(mine ? ghist[threadIdx.x] : 0u, s_warp, tot_all);
 	const uint32_t ls = block_excl_scan(total, s_warp, tot_all);
 	if (mine) {
+		// look back over earlier tiles, 8 descriptors per step: the loads of a step are independent,
+		// so a long run of tiles that have only published their aggregate costs one memory round trip
+		// per 8 tiles instead of one per tile
 		uint32_t excl = 0;
-		for (int t = (int)tile - 1; t >= 0; t--) {
-			volatile uint32_t* p = lookback + (size_t)t * 256 + threadIdx.x;
-			uint32_t v;
-			while (((v = *p) & (E3_LB_AGG | E3_LB_PREFIX)) == 0) __nanosleep(20);
-			excl += v & E3_LB_MASK;
-			if (v & E3_LB_PREFIX) break;
+		bool found = (tile == 0);
+		for (int t = (int)tile - 1; t >= 0 && !found; t -= 8) {
+			uint32_t v[8];
+#pragma unroll
+			for (int k = 0; k < 8; k++) v[k] = (t - k >= 0) ? lookback[(size_t)(t - k) * 256 + threadIdx.x] : E3_LB_PREFIX;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				if (found) break;
+				while ((v[k] & (E3_LB_AGG | E3_LB_PREFIX)) == 0) { __nanosleep(20); v[k] = lookback[(size_t)(t - k) * 256 + threadIdx.x]; }
+				excl += v[k] & E3_LB_MASK;
+				if (v[k] & E3_LB_PREFIX) found = true;
+			}
 		}
 		if (tile != 0) { __threadfence(); lookback[(size_t)tile * 256 + threadIdx.x] = (excl + total) | E3_LB_PREFIX; }
 		s_gpos[threadIdx.x] = gb + excl;
