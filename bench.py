@@ -286,9 +286,12 @@ def main():
             loss.backward()
         if world > 1 and sync_grads:
             from event_3dgs_b200 import parallel
-            # at SH degree 0 the fused path knows d(features_rest) == 0 on every rank: nothing to exchange
-            skip_rest = use_fused and pc.active_sh_degree == 0
-            parallel.allreduce_gradients([p for p in leaves if not (skip_rest and p is pc._features_rest)], world)
+            if use_fused:
+                # one collective over the flat gradient buffer (at SH degree 0 it does not even contain
+                # the identically-zero features_rest gradient)
+                parallel.allreduce_flat(pc._grad_flat, world)
+            else:
+                parallel.allreduce_gradients(leaves, world)
         return loss
 
     def timed(fn, steps):

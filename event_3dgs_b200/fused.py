@@ -152,10 +152,7 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     sts = [_forward_raw(pc, cam_train, bg), _forward_raw(pc, cam_now, bg, channels=ec), _forward_raw(pc, cam_next, bg, channels=ec)]
     out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
     D = int(pc.active_sh_degree)
-    grads = {"xyz": torch.empty_like(pc._xyz), "features_dc": torch.empty_like(pc._features_dc),
-             "opacity": torch.empty_like(pc._opacity), "scaling": torch.empty_like(pc._scaling),
-             "rotation": torch.empty_like(pc._rotation),
-             "features_rest": torch.empty_like(pc._features_rest) if D > 0 else _zeros_like_cached(pc._features_rest)}
+    grads = _alloc_grads(pc, c, D)
     d_mean2D = torch.empty_like(pc._xyz)
     _backward_raw(pc, sts[0], bg, seeds["image"], grads, False, d_mean2D)
     _backward_raw(pc, sts[1], bg, seeds["image_now"], grads, True)
@@ -166,7 +163,7 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     pc._opacity.grad = grads["opacity"]
     pc._scaling.grad = grads["scaling"]
     pc._rotation.grad = grads["rotation"]
-    c.grad = out[1].reshape(c.shape).clone()
+    _finish_c_grad(c, grads, out)
     loss = out[0]
     if return_pkg:
         vsp = torch.zeros_like(pc._xyz)
@@ -183,10 +180,7 @@ def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_
     out, seeds = event_loss_and_seeds(st_a.color, st_a.color, st_n.color, gt, c, deblur)
     seeds["image"].add_(seeds["image_now"])
     D = int(pc.active_sh_degree)
-    grads = {"xyz": torch.empty_like(pc._xyz), "features_dc": torch.empty_like(pc._features_dc),
-             "opacity": torch.empty_like(pc._opacity), "scaling": torch.empty_like(pc._scaling),
-             "rotation": torch.empty_like(pc._rotation),
-             "features_rest": torch.empty_like(pc._features_rest) if D > 0 else _zeros_like_cached(pc._features_rest)}
+    grads = _alloc_grads(pc, c, D)
     d_mean2D = torch.empty_like(pc._xyz)
     _backward_raw(pc, st_a, bg, seeds["image"], grads, False, d_mean2D)
     _backward_raw(pc, st_n, bg, seeds["image_next"], grads, True)
@@ -196,13 +190,42 @@ def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_
     pc._opacity.grad = grads["opacity"]
     pc._scaling.grad = grads["scaling"]
     pc._rotation.grad = grads["rotation"]
-    c.grad = out[1].reshape(c.shape).clone()
+    _finish_c_grad(c, grads, out)
     if return_pkg:
         vsp = torch.zeros_like(pc._xyz)
         vsp.grad = d_mean2D
         return out[0], {"render": st_a.color, "viewspace_points": vsp, "visibility_filter": st_a.radii > 0,
                         "radii": st_a.radii, "num_rendered": [st_a.R, st_n.R], "loss_terms": out}
     return out[0]
+
+
+def _alloc_grads(pc, c, D):
+    """All gradients of one iteration live in ONE flat buffer (segments padded to 16 bytes), so that
+    the multi-GPU trainer exchanges them with a single NCCL all-reduce (parallel.allreduce_flat);
+    the per-parameter tensors handed to .grad are views into it. Left on pc as `_grad_flat`."""
+    names = [("xyz", pc._xyz), ("features_dc", pc._features_dc), ("opacity", pc._opacity), ("scaling", pc._scaling),
+             ("rotation", pc._rotation)]
+    if D > 0:
+        names.append(("features_rest", pc._features_rest))
+    sizes = [(t.numel() + 3) // 4 * 4 for _, t in names]
+    flat = torch.empty(sum(sizes) + 4, dtype=torch.float32, device=pc._xyz.device)
+    grads, off = {}, 0
+    for (n, t), sz in zip(names, sizes):
+        grads[n] = flat[off:off + t.numel()].view(t.shape)
+        if sz != t.numel():
+            flat[off + t.numel():off + sz].zero_()
+        off += sz
+    grads["c"] = flat[off:off + 1]
+    flat[off + 1:off + 4].zero_()
+    if D == 0:
+        grads["features_rest"] = _zeros_like_cached(pc._features_rest)
+    pc._grad_flat = flat
+    return grads
+
+
+def _finish_c_grad(c, grads, out):
+    grads["c"].copy_(out[1:2])
+    c.grad = grads["c"].view(c.shape)
 
 
 _ZERO_CACHE = {}

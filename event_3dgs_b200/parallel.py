@@ -37,6 +37,21 @@ def allreduce_gradients(params, world=None, average=True):
             p.grad.div_(world)
 
 
+def allreduce_flat(flat, world=None):
+    """Mean over ranks of one flat gradient buffer (fused.py keeps all gradients of an iteration in
+    one): a single collective; NCCL averages in the reduction itself, gloo sums and divides."""
+    if not dist.is_initialized():
+        return
+    world = world or dist.get_world_size()
+    if world == 1:
+        return
+    if dist.get_backend() == "nccl":
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+    else:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat.div_(world)
+
+
 def allreduce_densification_stats(grad_norm_increment, denom_increment, max_radii2D):
     """In-place: SUM of the two accumulator increments, MAX of the screen radii."""
     if not dist.is_initialized() or dist.get_world_size() == 1:

@@ -42,7 +42,9 @@ def _worker(rank, world, port, out):
     gn, den, rad = parallel.densification_increments(vgrad, vis, radii)
     local = (gn.clone(), den.clone(), rad.clone())
     parallel.allreduce_densification_stats(gn, den, rad)
-    torch.save(dict(pairs=pairs, grads=[p.grad for p in params], stats=(gn, den, rad), local=local), out % rank)
+    flat = torch.arange(10, dtype=torch.float32) * (rank + 1)
+    parallel.allreduce_flat(flat, world)
+    torch.save(dict(flat=flat, pairs=pairs, grads=[p.grad for p in params], stats=(gn, den, rad), local=local), out % rank)
     dist.destroy_process_group()
 
 
@@ -51,6 +53,7 @@ def test_two_rank_gradient_and_stats_reduction(tmp_path):
     out = str(tmp_path / "r%d.pt")
     mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
     r = [torch.load(out % i) for i in range(world)]
+    assert torch.allclose(r[0]["flat"], torch.arange(10, dtype=torch.float32) * 1.5) and torch.equal(r[0]["flat"], r[1]["flat"])
     assert r[0]["pairs"] == [0, 2, 4] and r[1]["pairs"] == [1, 3, 5]
     # single-process result: mean over all 6 pairs of d/dp sum(p*(b+1)) = mean(b+1) = 3.5
     for g0, g1 in zip(r[0]["grads"], r[1]["grads"]):
