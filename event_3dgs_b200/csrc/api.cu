@@ -299,7 +299,7 @@ int e3_rasterize_backward_raw(
 }
 
 int e3_event_loss(int width, int height, const float* image, const float* image_now, const float* image_next,
-	const float* gt_now, const float* gt_next, const float* gt_intensity, const float* gt_blur, const float* c,
+	const void* gt_now, const void* gt_next, const void* gt_intensity, const void* gt_blur, int gt_is_u8, const float* c,
 	float upstream, int event_channels, void* scratch, size_t scratch_bytes, float* d_image, float* d_image_now,
 	float* d_image_next, float* out5, void* stream)
 {
@@ -310,7 +310,7 @@ int e3_event_loss(int width, int height, const float* image, const float* image_
 		!d_image_next || !out5)
 		return E3_ERR_BAD_ARGUMENT;
 	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_loss((size_t)width * height, image, image_now, image_next, gt_now, gt_next,
-		gt_intensity, gt_blur, c, upstream, event_channels, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
+		gt_intensity, gt_blur, gt_is_u8, c, upstream, event_channels, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
 	return 0;
 }
 

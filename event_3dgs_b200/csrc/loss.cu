@@ -28,11 +28,18 @@ __device__ __forceinline__ float luma_ev(const float* __restrict__ img, size_t i
 	return LUMA_R * __ldg(img + i) + LUMA_G * __ldg(img + N + i) + LUMA_B * __ldg(img + 2 * N + i);
 }
 
-__device__ __forceinline__ float luma3(const float* __restrict__ img, size_t i, size_t N)
+// GT frames may stay in the 8-bit form they have on disk (the reference converts them to fp32 /255
+// once at load time, utils/general_utils.py:21-27, and keeps 12 bytes per pixel resident)
+template <typename GT> __device__ __forceinline__ float gt_load(const GT* __restrict__ p, size_t i);
+template <> __device__ __forceinline__ float gt_load<float>(const float* __restrict__ p, size_t i) { return __ldg(p + i); }
+template <> __device__ __forceinline__ float gt_load<uint8_t>(const uint8_t* __restrict__ p, size_t i) { return (float)__ldg(p + i) / 255.0f; }
+
+template <typename GT>
+__device__ __forceinline__ float luma_gt(const GT* __restrict__ img, size_t i, size_t N)
 {
-	// utils/loss_utils.py:25, evaluated left to right like the PyTorch expression
-	return LUMA_R * __ldg(img + i) + LUMA_G * __ldg(img + N + i) + LUMA_B * __ldg(img + 2 * N + i);
+	return LUMA_R * gt_load<GT>(img, i) + LUMA_G * gt_load<GT>(img, N + i) + LUMA_B * gt_load<GT>(img, 2 * N + i);
 }
+
 
 __device__ __forceinline__ float sgn(float v) { return (v > 0.f) - (v < 0.f); }
 
@@ -51,10 +58,10 @@ __device__ __forceinline__ double block_sum(double v, double* sm)
 
 // sums[0] = sum |d - g|, [1] = #(g != 0), [2] = sum |image - gt_int| (3N terms),
 // [3] = sum |image - gt_blur|, [4] = sum sgn(d - g) * d
-template <int EC>
+template <int EC, typename GT>
 __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const float* __restrict__ image,
-	const float* __restrict__ image_now, const float* __restrict__ image_next, const float* __restrict__ gt_now,
-	const float* __restrict__ gt_next, const float* __restrict__ gt_int, const float* __restrict__ gt_blur,
+	const float* __restrict__ image_now, const float* __restrict__ image_next, const GT* __restrict__ gt_now,
+	const GT* __restrict__ gt_next, const GT* __restrict__ gt_int, const GT* __restrict__ gt_blur,
 	const float* __restrict__ c_ptr, double* __restrict__ sums)
 {
 	__shared__ double sm[8];
@@ -63,15 +70,15 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
 		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
-		const float g = (logf(luma3(gt_next, i, N) + EVT_EPS) - logf(luma3(gt_now, i, N) + EVT_EPS)) / 0.17f;
+		const float g = (logf(luma_gt<GT>(gt_next, i, N) + EVT_EPS) - logf(luma_gt<GT>(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		s0 += fabsf(d - g);
 		s1 += (g != 0.f) ? 1.0 : 0.0;
 		s4 += sgn(d - g) * d;
 #pragma unroll
 		for (int ch = 0; ch < 3; ch++) {
 			const float v = __ldg(image + ch * N + i);
-			s2 += fabsf(v - __ldg(gt_int + ch * N + i));
-			if (gt_blur) s3 += fabsf(v - __ldg(gt_blur + ch * N + i));
+			s2 += fabsf(v - gt_load<GT>(gt_int, ch * N + i));
+			if (gt_blur) s3 += fabsf(v - gt_load<GT>(gt_blur, ch * N + i));
 		}
 	}
 	s0 = block_sum(s0, sm); s1 = block_sum(s1, sm); s2 = block_sum(s2, sm);
@@ -84,10 +91,10 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 
 // out[0] = loss, out[1] = dL/dc, out[2] = loss1 (event L1), out[3] = loss2 (intensity L1),
 // out[4] = fraction of pixels with a non-zero GT event difference
-template <int EC>
+template <int EC, typename GT>
 __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const float* __restrict__ image,
-	const float* __restrict__ image_now, const float* __restrict__ image_next, const float* __restrict__ gt_now,
-	const float* __restrict__ gt_next, const float* __restrict__ gt_int, const float* __restrict__ gt_blur,
+	const float* __restrict__ image_now, const float* __restrict__ image_next, const GT* __restrict__ gt_now,
+	const GT* __restrict__ gt_next, const GT* __restrict__ gt_int, const GT* __restrict__ gt_blur,
 	const float* __restrict__ c_ptr, const double* __restrict__ sums, float upstream, float* __restrict__ d_image,
 	float* __restrict__ d_now, float* __restrict__ d_next, float* __restrict__ out)
 {
@@ -109,7 +116,7 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
 		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
-		const float g = (logf(luma3(gt_next, i, N) + EVT_EPS) - logf(luma3(gt_now, i, N) + EVT_EPS)) / 0.17f;
+		const float g = (logf(luma_gt<GT>(gt_next, i, N) + EVT_EPS) - logf(luma_gt<GT>(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		const float s = sgn(d - g);
 		const float dy2 = k1 * s / (c * (y2 + EVT_EPS));
 		const float dy1 = -k1 * s / (c * (y1 + EVT_EPS));
@@ -121,8 +128,8 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 #pragma unroll
 		for (int ch = 0; ch < 3; ch++) {
 			const float v = __ldg(image + ch * N + i);
-			float gr = k2 * sgn(v - __ldg(gt_int + ch * N + i));
-			if (gt_blur) gr += k3 * sgn(v - __ldg(gt_blur + ch * N + i));
+			float gr = k2 * sgn(v - gt_load<GT>(gt_int, ch * N + i));
+			if (gt_blur) gr += k3 * sgn(v - gt_load<GT>(gt_blur, ch * N + i));
 			d_image[ch * N + i] = gr;
 		}
 	}
@@ -130,22 +137,28 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 
 }  // namespace
 
+template <int EC, typename GT>
+static void launch_loss(int grid, size_t N, const float* image, const float* image_now, const float* image_next, const void* gt_now,
+	const void* gt_next, const void* gt_int, const void* gt_blur, const float* c_ptr, float upstream, double* sums, float* d_image,
+	float* d_now, float* d_next, float* out, cudaStream_t st)
+{
+	event_loss_reduce_kernel<EC, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
+		(const GT*)gt_int, (const GT*)gt_blur, c_ptr, sums);
+	event_loss_seed_kernel<EC, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
+		(const GT*)gt_int, (const GT*)gt_blur, c_ptr, sums, upstream, d_image, d_now, d_next, out);
+}
+
 cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
-	const float* gt_now, const float* gt_next, const float* gt_int, const float* gt_blur, const float* c_ptr,
+	const void* gt_now, const void* gt_next, const void* gt_int, const void* gt_blur, int gt_is_u8, const float* c_ptr,
 	float upstream, int event_channels, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st)
 {
 	cudaError_t e = cudaMemsetAsync(sums, 0, 8 * sizeof(double), st);
 	if (e != cudaSuccess) return e;
 	const int grid = (int)min((size_t)148 * 8, (N + 255) / 256);
-	if (event_channels == 1) {
-		event_loss_reduce_kernel<1><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums);
-		event_loss_seed_kernel<1><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums,
-			upstream, d_image, d_now, d_next, out);
-	} else {
-		event_loss_reduce_kernel<3><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums);
-		event_loss_seed_kernel<3><<<grid, 256, 0, st>>>(N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, sums,
-			upstream, d_image, d_now, d_next, out);
-	}
+#define ARGS grid, N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, upstream, sums, d_image, d_now, d_next, out, st
+	if (event_channels == 1) { if (gt_is_u8) launch_loss<1, uint8_t>(ARGS); else launch_loss<1, float>(ARGS); }
+	else { if (gt_is_u8) launch_loss<3, uint8_t>(ARGS); else launch_loss<3, float>(ARGS); }
+#undef ARGS
 	g_e3_launches += 2;
 	return cudaGetLastError();
 }

@@ -95,10 +95,16 @@ def event_loss_and_seeds(image, image_now, image_next, gt, c, deblur=False, upst
     out = torch.empty(5, dtype=torch.float32, device=dev)
     scratch = torch.empty(8, dtype=torch.float64, device=dev)
     blur = gt["blurry"] if deblur else None
+    frames = [gt["event_now"], gt["event_next"], gt["intensity"]] + ([blur] if blur is not None else [])
+    u8 = frames[0].dtype == torch.uint8
+    for f in frames:
+        if f.dtype != (torch.uint8 if u8 else torch.float32) or not f.is_contiguous() or tuple(f.shape) != (3, H, W):
+            raise RuntimeError("event_loss_and_seeds: GT frames must be contiguous [3,H,W], all float32 or all uint8")
     with torch.cuda.device(dev):
         code = L.e3_event_loss(W, H, image.data_ptr(), image_now.data_ptr(), image_next.data_ptr(),
                                gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr(),
-                               None if blur is None else blur.data_ptr(), c.data_ptr(), float(upstream), ec, scratch.data_ptr(), 64,
+                               None if blur is None else blur.data_ptr(), int(u8), c.data_ptr(), float(upstream), ec,
+                               scratch.data_ptr(), 64,
                                seeds["image"].data_ptr(), seeds["image_now"].data_ptr(), seeds["image_next"].data_ptr(),
                                out.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
     _lib.check(code)
@@ -127,7 +133,7 @@ def same_view(cam_a, cam_b):
 
 
 def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
-                             dedupe_views=False, gray_event_views=True):
+                             dedupe_views=False, gray_event_views=True, gt_ready=None):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
@@ -141,15 +147,19 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     gray_event_views: render the two event views with one channel, the luma that
     differentialable_event_simu takes of them anyway (utils/loss_utils.py:24-28,240-241); the
     algebraic rewrite behind the reference's --gray idea. Equal to the
-    3-channel route up to fp32 rounding; False reproduces the 3-channel renders exactly."""
+    3-channel route up to fp32 rounding; False reproduces the 3-channel renders exactly.
+
+    gt_ready: optional torch.cuda.Event recorded after the GT frames were copied to the device on
+    another stream; the loss waits for it, so the host-to-device copy overlaps the three renders."""
     if dedupe_views and same_view(cam_train, cam_now):
-        return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg)
-    for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg,
-              gt["event_now"], gt["event_next"], gt["intensity"]):
+        return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg, gt_ready)
+    for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("event_3dgs_b200.fused: tensors must be contiguous float32 CUDA tensors")
     ec = 1 if gray_event_views else 3
     sts = [_forward_raw(pc, cam_train, bg), _forward_raw(pc, cam_now, bg, channels=ec), _forward_raw(pc, cam_next, bg, channels=ec)]
+    if gt_ready is not None:
+        torch.cuda.current_stream(pc._xyz.device).wait_event(gt_ready)
     out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
     D = int(pc.active_sh_degree)
     grads = _alloc_grads(pc, c, D)
@@ -174,9 +184,11 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     return loss
 
 
-def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg):
+def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg, gt_ready=None):
     st_a = _forward_raw(pc, cam_a, bg)
     st_n = _forward_raw(pc, cam_next, bg)
+    if gt_ready is not None:
+        torch.cuda.current_stream(pc._xyz.device).wait_event(gt_ready)
     out, seeds = event_loss_and_seeds(st_a.color, st_a.color, st_n.color, gt, c, deblur)
     seeds["image"].add_(seeds["image_now"])
     D = int(pc.active_sh_degree)

@@ -173,7 +173,9 @@ E3_API int e3_rasterize_backward_raw(
 /* Event loss of train.py:165-203 (with utils/loss_utils.py:24-28, 234-249, 270-271), value and
  * backward seeds in two streaming kernels. Inputs are [3,H,W] float images: the three renders
  * (image = intensity view, image_now / image_next = event views index / index+1), the GT event
- * frames, the GT intensity frame and, for --deblur, the blurry frame (else NULL). `c` points to the
+ * frames, the GT intensity frame and, for --deblur, the blurry frame (else NULL). The four GT
+ * frames are float32 in [0,1] (gt_is_u8 = 0) or the raw 8-bit pixels (gt_is_u8 = 1; the kernel
+ * applies the reference's /255, utils/general_utils.py:21-27). `c` points to the
  * learnable event threshold on the device (train.py:71,165); the GT threshold is the constant 0.17
  * (train.py:170). `upstream` scales all gradients (1 for loss.backward()). event_channels = 3:
  * image_now / image_next and their seeds are [3,H,W]; 1: they are single-channel luma renders
@@ -181,8 +183,8 @@ E3_API int e3_rasterize_backward_raw(
  * 8-byte aligned device memory. Outputs: the three seeds dL/dimage* [3,H,W] and
  * out5 = { loss, dL/dc, event L1, intensity L1, fraction of pixels with non-zero GT event }. */
 E3_API int e3_event_loss(int width, int height, const float* image, const float* image_now,
-	const float* image_next, const float* gt_now, const float* gt_next, const float* gt_intensity,
-	const float* gt_blur, const float* c, float upstream, int event_channels, void* scratch,
+	const float* image_next, const void* gt_now, const void* gt_next, const void* gt_intensity,
+	const void* gt_blur, int gt_is_u8, const float* c, float upstream, int event_channels, void* scratch,
 	size_t scratch_bytes, float* d_image, float* d_image_now, float* d_image_next, float* out5,
 	void* stream);
 

@@ -86,6 +86,13 @@ def test_event_loss_kernel_vs_numpy_oracle_and_golden(cuda_dev):
     assert abs(o1[0].item() - o2[0].item()) < 1e-7
     assert rel_err((2 * s1["image_now"]).cpu().numpy(), s2["image_now"].cpu().numpy()) < 1e-6
     assert abs(2 * o1[1].item() - o2[1].item()) <= 1e-6 * abs(o2[1].item())
+    # 8-bit GT frames (as on disk) give exactly what their /255 float32 form gives
+    g8 = {k: torch.tensor(rng.integers(0, 256, (3, 720, 1280), dtype=np.uint8)).to(cuda_dev) for k in gt}
+    gf = {k: (v.float() / 255.0) for k, v in g8.items()}
+    o8, s8 = fused.event_loss_and_seeds(*imgs, g8, c, True)
+    of, sf = fused.event_loss_and_seeds(*imgs, gf, c, True)
+    assert torch.equal(s8["image"], sf["image"]) and torch.equal(s8["image_next"], sf["image_next"])
+    assert abs(o8[0].item() - of[0].item()) <= 1e-7 * abs(of[0].item())
 
 
 def test_dist2_matches_bruteforce_oracle(cuda_dev):
