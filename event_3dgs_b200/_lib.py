@@ -32,6 +32,8 @@ SIGNATURES = {
     "e3_rasterize_backward_raw": (_i, [_i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
                                        _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _f, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
+    "e3_l1_ssim_scratch_bytes": (_sz, [_i, _i, _i]),
+    "e3_l1_ssim_loss": (_i, [_i, _i, _i, _vp, _vp, _i, _f, _f, _vp, _sz, _vp, _vp, _vp]),
     "e3_mark_visible": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "e3_dist2_scratch_bytes": (_sz, [_i]),
     "e3_dist2": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),

@@ -339,6 +339,24 @@ int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch
 	return 0;
 }
 
+size_t e3_l1_ssim_scratch_bytes(int width, int height, int gray)
+{
+	return (width > 0 && height > 0) ? e3_l1_ssim_scratch_words(width, height, gray != 0) * sizeof(float) : 0;
+}
+
+int e3_l1_ssim_loss(int width, int height, int gray, const float* image, const void* gt, int gt_is_u8, float lambda_dssim,
+	float upstream, void* scratch, size_t scratch_bytes, float* d_image, float* out3, void* stream)
+{
+	cudaStream_t st = (cudaStream_t)stream;
+	const int debug = 0;
+	if (width <= 0 || height <= 0 || !image || !gt || !scratch || !d_image || !out3 || (reinterpret_cast<size_t>(scratch) & 7) ||
+		scratch_bytes < e3_l1_ssim_scratch_bytes(width, height, gray))
+		return E3_ERR_BAD_ARGUMENT;
+	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_l1_ssim(width, height, gray != 0, image, gt, gt_is_u8 != 0, lambda_dssim, upstream,
+		static_cast<float*>(scratch), d_image, out3, st));
+	return 0;
+}
+
 size_t e3_dist2_scratch_bytes(int P)
 {
 	return P > 0 ? e3_knn_scratch_layout(P, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) : 0;

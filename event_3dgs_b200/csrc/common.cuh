@@ -167,3 +167,8 @@ int e3_knn_grid_dim(int P);
 size_t e3_knn_scratch_layout(int P, uint32_t** keys, uint32_t** vals, uint32_t** counts, uint32_t** scan_tmp, uint2** ranges,
 	float4** sorted, uint32_t** bbox, void** grid, char* base);
 cudaError_t e3_launch_dist2(int P, const float* pts, float* out, char* scratch, cudaStream_t st);
+
+// ssim.cu
+size_t e3_l1_ssim_scratch_words(int W, int H, bool gray);
+cudaError_t e3_launch_l1_ssim(int W, int H, bool gray, const float* img, const void* gt, bool gt_is_u8, float lambda,
+	float upstream, float* scratch, float* d_image, float* out3, cudaStream_t st);

@@ -253,3 +253,50 @@ def _zeros_like_cached(t):
         _ZERO_CACHE.clear()
         _ZERO_CACHE[key] = z
     return z
+
+
+def l1_ssim_loss_and_seed(image, gt_image, lambda_dssim=0.2, gray=False, upstream=1.0):
+    """e3_l1_ssim_loss: the loss of the non-event branches of train.py (:213-223 with gray=True,
+    :292-296 with gray=False). Returns (out3 tensor [loss, L1, SSIM], dL/dimage [3,H,W])."""
+    L = _lib.lib()
+    dev = image.device
+    _, H, W = image.shape
+    u8 = gt_image.dtype == torch.uint8
+    if tuple(image.shape) != (3, H, W) or tuple(gt_image.shape) != (3, H, W) or not image.is_contiguous() or \
+            not gt_image.is_contiguous() or image.dtype != torch.float32 or (not u8 and gt_image.dtype != torch.float32):
+        raise RuntimeError("l1_ssim_loss_and_seed: image float32 [3,H,W], gt float32 or uint8 [3,H,W], contiguous")
+    nb = L.e3_l1_ssim_scratch_bytes(W, H, int(bool(gray)))
+    scratch = torch.empty((nb + 7) // 8, dtype=torch.float64, device=dev)
+    seed = torch.empty_like(image)
+    out = torch.empty(3, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.e3_l1_ssim_loss(W, H, int(bool(gray)), image.data_ptr(), gt_image.data_ptr(), int(u8), float(lambda_dssim),
+                                     float(upstream), scratch.data_ptr(), scratch.numel() * 8, seed.data_ptr(), out.data_ptr(),
+                                     torch.cuda.current_stream(dev).cuda_stream))
+    return out, seed
+
+
+def frame_iteration_backward(pc, cam, gt_image, bg, lambda_dssim=0.2, gray=False, return_pkg=False):
+    """The non-event iteration of train.py (one render, L1 + SSIM loss, loss.backward()): the
+    --gray branch (:213-223) with gray=True, the RGB branch (:292-296) with gray=False. Sets .grad
+    on the six leaf tensors of pc and returns the loss."""
+    st = _forward_raw(pc, cam, bg)
+    out, seed = l1_ssim_loss_and_seed(st.color, gt_image, lambda_dssim, gray)
+    D = int(pc.active_sh_degree)
+    dummy_c = torch.zeros(1, device=pc._xyz.device)
+    grads = _alloc_grads(pc, dummy_c, D)
+    d_mean2D = torch.empty_like(pc._xyz)
+    _backward_raw(pc, st, bg, seed, grads, False, d_mean2D)
+    grads["c"].zero_()
+    pc._xyz.grad = grads["xyz"]
+    pc._features_dc.grad = grads["features_dc"]
+    pc._features_rest.grad = grads["features_rest"]
+    pc._opacity.grad = grads["opacity"]
+    pc._scaling.grad = grads["scaling"]
+    pc._rotation.grad = grads["rotation"]
+    if return_pkg:
+        vsp = torch.zeros_like(pc._xyz)
+        vsp.grad = d_mean2D
+        return out[0], {"render": st.color, "viewspace_points": vsp, "visibility_filter": st.radii > 0, "radii": st.radii,
+                        "num_rendered": [st.R], "loss_terms": out}
+    return out[0]

@@ -176,3 +176,38 @@ def event_iteration(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, r
     loss = event_loss(image, image_now, image_next, gt["event_now"], gt["event_next"], gt["intensity"], c,
                       gt["blurry"] if deblur else None)
     return loss, pkg
+
+
+# ---- the non-event losses (utils/loss_utils.py:18-23, 40-48, 359-418), restated for tests/bench ----
+def rgb_to_grayscale(image):
+    return (0.299 * image[0, :, :] + 0.587 * image[1, :, :] + 0.114 * image[2, :, :]).unsqueeze(0)
+
+
+def _window(channel, like):
+    import math as _m
+    g = torch.tensor([_m.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g = (g / g.sum()).unsqueeze(1)
+    w2 = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0)
+    return w2.expand(channel, 1, 11, 11).contiguous().to(like)
+
+
+def ssim(img1, img2):
+    channel = img1.size(-3)
+    w = _window(channel, img1)
+    F = torch.nn.functional
+    mu1, mu2 = F.conv2d(img1, w, padding=5, groups=channel), F.conv2d(img2, w, padding=5, groups=channel)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(img1 * img1, w, padding=5, groups=channel) - mu1_sq
+    s2 = F.conv2d(img2 * img2, w, padding=5, groups=channel) - mu2_sq
+    s12 = F.conv2d(img1 * img2, w, padding=5, groups=channel) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    return (((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))).mean()
+
+
+def l1_ssim_loss(image, gt, lambda_dssim=0.2, gray=False):
+    """train.py:213-223 (gray) / :292-296 (RGB)."""
+    if gray:
+        a, b = rgb_to_grayscale(image), rgb_to_grayscale(gt)
+    else:
+        a, b = image, gt
+    return (1.0 - lambda_dssim) * torch.abs(a - b).mean() + lambda_dssim * (1.0 - ssim(a, b))

@@ -207,6 +207,20 @@ typedef struct e3_adam_group {
 E3_API int e3_adam_step(const e3_adam_group* groups_host, int num_groups, int step, double beta1,
 	double beta2, void* stream);
 
+/* L1 + SSIM loss of the two non-event training branches, value and backward seed:
+ * loss = (1 - lambda_dssim) * L1 + lambda_dssim * (1 - SSIM), with the 11x11 Gaussian-window SSIM
+ * of utils/loss_utils.py:359-418 (sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2).
+ * gray = 1: the `--gray` branch of train.py:213-223 (l1_loss_gray + ssim_gray on the luma
+ * 0.299 R + 0.587 G + 0.114 B, utils/loss_utils.py:18-23,40-48,368-385);
+ * gray = 0: the RGB branch of train.py:292-296 (l1_loss + ssim over the 3 channels).
+ * image is the render [3,H,W] float; gt the ground-truth frame [3,H,W], float32 or 8-bit
+ * (gt_is_u8, /255 applied). scratch: e3_l1_ssim_scratch_bytes() of 8-byte aligned device memory.
+ * Outputs: d_image [3,H,W] = upstream * dloss/dimage, out3 = { loss, L1, SSIM }. */
+E3_API size_t e3_l1_ssim_scratch_bytes(int width, int height, int gray);
+E3_API int e3_l1_ssim_loss(int width, int height, int gray, const float* image, const void* gt,
+	int gt_is_u8, float lambda_dssim, float upstream, void* scratch, size_t scratch_bytes,
+	float* d_image, float* out3, void* stream);
+
 /* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
  * rasterizer_impl.cu:54-66,141-153): present[i] = view-space z > 0.2. present is uint8[P]. */
 E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,

@@ -58,6 +58,26 @@ def event_case(seed, H, W, deblur, zero_frac):
                 d_c=np.float32(c.grad.item()), img_diff=img_diff.detach().numpy(), gt_diff=gt_image.numpy())
 
 
+def ssim_case(seed, H, W, gray):
+    """train.py:213-223 (--gray, no --event) and train.py:292-296 (RGB), lambda_dssim = 0.2."""
+    g = torch.Generator().manual_seed(seed)
+    yy, xx = torch.meshgrid(torch.linspace(0, 1, H), torch.linspace(0, 1, W), indexing="ij")
+    base = torch.stack([0.5 + 0.4 * torch.sin(6 * xx + k) * torch.cos(5 * yy - k) for k in range(3)])
+    gt = torch.round((base + 0.05 * torch.randn(3, H, W, generator=g)).clamp(0, 1) * 255) / 255
+    image = (base + 0.1 * torch.randn(3, H, W, generator=g)).clamp(0, 1).requires_grad_()
+    lam = 0.2
+    if gray:
+        Ll1 = lu.l1_loss_gray(image, gt)
+        ss = lu.ssim_gray(image, gt)
+    else:
+        Ll1 = lu.l1_loss(image, gt)
+        ss = lu.ssim(image, gt)
+    loss = (1.0 - lam) * Ll1 + lam * (1.0 - ss)
+    loss.backward()
+    return dict(image=image.detach().numpy(), gt=gt.numpy(), gray=np.bool_(gray), lam=np.float32(lam),
+                loss=np.float32(loss.item()), l1=np.float32(Ll1.item()), ssim=np.float32(ss.item()), d_image=image.grad.numpy())
+
+
 def sh_case(seed, P):
     g = torch.Generator().manual_seed(seed)
     sh = torch.randn(P, 3, 16, generator=g)
@@ -75,4 +95,6 @@ if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "event_loss_b.npz"), **event_case(1, 17, 33, True, 0.3))
     np.savez_compressed(os.path.join(HERE, "event_loss_c.npz"), **event_case(2, 16, 16, False, 1.0))   # no events at all
     np.savez_compressed(os.path.join(HERE, "eval_sh.npz"), **sh_case(3, 64))
+    np.savez_compressed(os.path.join(HERE, "l1_ssim_gray.npz"), **ssim_case(4, 37, 50, True))
+    np.savez_compressed(os.path.join(HERE, "l1_ssim_rgb.npz"), **ssim_case(5, 33, 20, False))
     print("golden vectors written to", HERE)

@@ -75,3 +75,14 @@ def test_oracle_sh_colour_matches_reference_eval_sh():
         ref = np.maximum(d["rgb%d" % deg] + 0.5, 0.0)       # gaussian_renderer/__init__.py:81
         assert np.allclose(dirs, d["dirs"], atol=1e-5)
         assert rel_err(st["rgb"][vis], ref[vis]) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["l1_ssim_gray", "l1_ssim_rgb"])
+def test_pipeline_l1_ssim_matches_reference(name):
+    from event_3dgs_b200 import pipeline as pl
+    d = np.load(os.path.join(G, name + ".npz"))
+    image = torch.tensor(d["image"]).requires_grad_()
+    loss = pl.l1_ssim_loss(image, torch.tensor(d["gt"]), float(d["lam"]), bool(d["gray"]))
+    loss.backward()
+    assert abs(loss.item() - float(d["loss"])) <= 1e-6 * abs(float(d["loss"]))
+    assert rel_err(image.grad.numpy(), d["d_image"]) < 1e-5
