@@ -133,7 +133,7 @@ def same_view(cam_a, cam_b):
 
 
 def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
-                             dedupe_views=False, gray_event_views=True, gt_ready=None):
+                             dedupe_views=False, gray_event_views=True, gt_ready=None, accumulate=False):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
@@ -150,8 +150,17 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     3-channel route up to fp32 rounding; False reproduces the 3-channel renders exactly.
 
     gt_ready: optional torch.cuda.Event recorded after the GT frames were copied to the device on
-    another stream; the loss waits for it, so the host-to-device copy overlaps the three renders."""
+    another stream; the loss waits for it, so the host-to-device copy overlaps the three renders.
+
+    accumulate: add this view-pair's gradients to the ones the previous call left (several pairs per
+    optimizer step, e.g. BASELINE config c5 with 64 pairs per step); the returned loss is this
+    pair's. The caller divides by the number of pairs (or lets parallel.allreduce_flat average over
+    ranks and scales the rest)."""
+    if accumulate and getattr(pc, "_grad_flat", None) is None:
+        raise RuntimeError("accumulate=True needs the gradients of a previous call")
     if dedupe_views and same_view(cam_train, cam_now):
+        if accumulate:
+            raise RuntimeError("accumulate=True is not combined with dedupe_views")
         return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg, gt_ready)
     for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
@@ -162,11 +171,14 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
         torch.cuda.current_stream(pc._xyz.device).wait_event(gt_ready)
     out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
     D = int(pc.active_sh_degree)
-    grads = _alloc_grads(pc, c, D)
-    d_mean2D = torch.empty_like(pc._xyz)
-    _backward_raw(pc, sts[0], bg, seeds["image"], grads, False, d_mean2D)
+    grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D)
+    d_mean2D = None if accumulate else torch.empty_like(pc._xyz)
+    _backward_raw(pc, sts[0], bg, seeds["image"], grads, accumulate, d_mean2D)
     _backward_raw(pc, sts[1], bg, seeds["image_now"], grads, True)
     _backward_raw(pc, sts[2], bg, seeds["image_next"], grads, True)
+    if accumulate:
+        grads["c"].add_(out[1:2])
+        return out[0]
     pc._xyz.grad = grads["xyz"]
     pc._features_dc.grad = grads["features_dc"]
     pc._features_rest.grad = grads["features_rest"]
@@ -232,6 +244,7 @@ def _alloc_grads(pc, c, D):
     if D == 0:
         grads["features_rest"] = _zeros_like_cached(pc._features_rest)
     pc._grad_flat = flat
+    pc._grad_views = grads
     return grads
 
 

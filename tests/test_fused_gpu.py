@@ -232,3 +232,17 @@ def test_frame_iteration_matches_dropin_autograd(cuda_dev):
         # borderline alpha >= 1/255 or radius decision may flip for single Gaussians
         for a, b in zip(ga, gb):
             assert rel_err(b.cpu().numpy(), a.cpu().numpy()) < 5e-4
+
+
+def test_accumulate_over_view_pairs(cuda_dev):
+    from event_3dgs_b200 import fused
+    pl, pc, cams, gt, bg, c = _setup(20_000, 200, 120, 1, False)
+    leaves = pc.leaves() + [c]
+    fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
+    g1 = [p.grad.clone() for p in leaves]
+    fused.event_iteration_backward(pc, cams[4], cams[4], cams[5], gt, c, bg)
+    g2 = [p.grad.clone() for p in leaves]
+    fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
+    fused.event_iteration_backward(pc, cams[4], cams[4], cams[5], gt, c, bg, accumulate=True)
+    for p, a, b in zip(leaves, g1, g2):
+        assert rel_err(p.grad.cpu().numpy(), (a + b).cpu().numpy(), 1e-20) < 1e-4
