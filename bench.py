@@ -419,8 +419,16 @@ def main():
         per_launch_ms = t_ms / n
         algo = float(np.mean([bytes_bwd_blend(P, r, N, T) for r in Rs]))
         ach = algo / (per_launch_ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            if cfg_name == "c3" and "render_bwd_kernel<1>" in tj:
+                traffic = tj["render_bwd_kernel<1>"]["dram_bytes_per_launch"]
+                traffic_src = "profiles/r1_traffic.json (ncu --set full, c3, render_bwd_kernel<1>: the single-channel variant, 2 of the 3 launches per step)"
+        except Exception:
+            pass
         line["roofline"] = {"bound": "hbm", "kernel": "render_bwd_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                            "frac": ach / peak, "traffic": None, "launch_ms": per_launch_ms, "launches": int(n),
+                            "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src, "launch_ms": per_launch_ms, "launches": int(n),
                             "algorithmic_bytes_per_launch": algo,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                             "note": "the blend kernels are issue/latency bound, not HBM bound; see DESIGN.md"}

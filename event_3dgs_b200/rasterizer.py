@@ -37,6 +37,14 @@ def _ptr(t):
     return t.data_ptr()
 
 
+def _check_device(dev, **tensors):
+    """Every non-empty tensor must live on the device of means3D (a host pointer handed to a
+    kernel would fault asynchronously; the reference has the same requirement, implicitly)."""
+    for name, t in tensors.items():
+        if t is not None and t.numel() != 0 and t.device != dev:
+            raise RuntimeError("event_3dgs_b200: `%s` is on %s but means3D is on %s" % (name, t.device, dev))
+
+
 def _f32c(t):
     if t is None or t.numel() == 0:
         return t
@@ -62,6 +70,8 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
     P = means3D.size(0)
     H, W = int(image_height), int(image_width)
     dev = means3D.device
+    _check_device(dev, bg=bg, colors_precomp=colors_precomp, opacities=opacities, scales=scales, rotations=rotations,
+                  cov3Ds_precomp=cov3Ds_precomp, viewmatrix=viewmatrix, projmatrix=projmatrix, sh=sh, campos=campos)
     have_colors = colors_precomp is not None and colors_precomp.numel() != 0
     C = int(colors_precomp.size(1)) if have_colors else 3
     M = int(sh.size(1)) if (sh is not None and sh.numel() != 0) else 0

@@ -226,6 +226,9 @@ def test_dropin_api_autograd_and_errors(gc):
         rast(means3D=means, means2D=m2d, opacities=op, scales=sc, rotations=rot)
     with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
         rast(means3D=means, means2D=m2d, opacities=op, colors_precomp=col, scales=sc)
+    bad = settings._replace(bg=t["bg"].cpu())
+    with pytest.raises(RuntimeError, match="`bg` is on cpu"):
+        GaussianRasterizer(bad)(means3D=means, means2D=m2d, opacities=op, colors_precomp=col, scales=sc, rotations=rot)
     with pytest.raises(RuntimeError, match="means3D must have dimensions"):
         rast(means3D=means.reshape(-1), means2D=m2d, opacities=op, colors_precomp=col, scales=sc, rotations=rot)
 
