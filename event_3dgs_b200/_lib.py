@@ -29,6 +29,8 @@ SIGNATURES = {
                                    _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "e3_rasterize_forward_raw": (_i, [ALLOC_FN, _vp, ALLOC_FN, _vp, ALLOC_FN, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp,
                                       _vp, _f, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp, ctypes.POINTER(_i)]),
+    "e3_rasterize_forward_raw_ws": (_i, [_vp, _vp, _sz, _vp, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp,
+                                         _vp, _f, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp]),
     "e3_rasterize_backward_raw": (_i, [_i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
                                        _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "e3_event_loss": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _f, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
@@ -57,6 +59,32 @@ class AdamGroup(ctypes.Structure):
                 ("exp_avg_sq", ctypes.c_void_p), ("n", ctypes.c_ulonglong), ("lr", ctypes.c_float), ("eps", ctypes.c_float)]
 
 
+class View(ctypes.Structure):
+    """e3_view of include/event3dgs.h."""
+    _fields_ = [("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p), ("cam_pos", ctypes.c_void_p),
+                ("tan_fovx", ctypes.c_float), ("tan_fovy", ctypes.c_float), ("channels", ctypes.c_int),
+                ("geometry_buffer", ctypes.c_void_p), ("binning_buffer", ctypes.c_void_p), ("image_buffer", ctypes.c_void_p),
+                ("out_color", ctypes.c_void_p), ("radii", ctypes.c_void_p), ("seed", ctypes.c_void_p),
+                ("num_rendered_host", ctypes.c_void_p)]
+
+
+class EventIterationArgs(ctypes.Structure):
+    """e3_event_iteration_args of include/event3dgs.h."""
+    _fields_ = [("P", ctypes.c_int), ("active_sh_degree", ctypes.c_int), ("width", ctypes.c_int), ("height", ctypes.c_int),
+                ("binning_capacity", ctypes.c_ulonglong), ("scale_modifier", ctypes.c_float), ("accumulate", ctypes.c_int),
+                ("background", ctypes.c_void_p),
+                ("xyz", ctypes.c_void_p), ("features_dc", ctypes.c_void_p), ("features_rest", ctypes.c_void_p),
+                ("opacity_logits", ctypes.c_void_p), ("log_scales", ctypes.c_void_p), ("raw_rotations", ctypes.c_void_p),
+                ("d_xyz", ctypes.c_void_p), ("d_features_dc", ctypes.c_void_p), ("d_features_rest", ctypes.c_void_p),
+                ("d_opacity_logits", ctypes.c_void_p), ("d_log_scales", ctypes.c_void_p), ("d_raw_rotations", ctypes.c_void_p),
+                ("d_mean2D", ctypes.c_void_p),
+                ("views", View * 3),
+                ("gt_now", ctypes.c_void_p), ("gt_next", ctypes.c_void_p), ("gt_intensity", ctypes.c_void_p), ("gt_blur", ctypes.c_void_p),
+                ("gt_is_u8", ctypes.c_int), ("c", ctypes.c_void_p), ("out5", ctypes.c_void_p), ("loss_scratch", ctypes.c_void_p),
+                ("wait_before_loss_event", ctypes.c_void_p), ("forwards_done_event", ctypes.c_void_p)]
+
+
+SIGNATURES["e3_event_iteration"] = (_i, [ctypes.POINTER(EventIterationArgs), _vp])
 SIGNATURES["e3_adam_step"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, _vp])
 
 _lib = None

@@ -114,7 +114,12 @@ size_t e3_binning_bytes(int num_rendered)
 	return (size_t)end + 256;
 }
 
+// Caller-owned workspace of the no-sync path (e3_rasterize_forward_raw_ws): three buffers sized by
+// the caller, the binning one for `cap` instances; R is copied to `r_host` asynchronously.
+struct WsMode { char* g; char* b; size_t cap; char* i; int* r_host; };
+
 static int forward_impl(
+	const WsMode* ws,
 	e3_alloc_fn geometry_alloc, void* geometry_ctx,
 	e3_alloc_fn binning_alloc, void* binning_ctx,
 	e3_alloc_fn image_alloc, void* image_ctx,
@@ -131,9 +136,10 @@ static int forward_impl(
 	if (num_rendered_host) *num_rendered_host = 0;
 	if (P < 0 || width <= 0 || height <= 0 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
 	if (P == 0) return 0;
-	if (!geometry_alloc || !binning_alloc || !image_alloc || !means3D || !opacities || !background ||
-		!viewmatrix || !projmatrix || !out_color || !radii || !num_rendered_host)
+	if ((!ws && (!geometry_alloc || !binning_alloc || !image_alloc || !num_rendered_host)) || !means3D || !opacities || !background ||
+		!viewmatrix || !projmatrix || !out_color || !radii)
 		return E3_ERR_BAD_ARGUMENT;
+	if (ws && (!ws->g || !ws->i || (ws->cap > 0 && !ws->b) || !ws->r_host || ws->cap > 0x7fffffffu)) return E3_ERR_BAD_ARGUMENT;
 	if (!colors_precomp && (!shs || !cam_pos)) return E3_ERR_BAD_ARGUMENT;
 	if (!colors_precomp && channels != 3 && !raw) return E3_ERR_UNSUPPORTED;
 	if (!cov3D_precomp && (!scales || !rotations)) return E3_ERR_BAD_ARGUMENT;
@@ -141,10 +147,10 @@ static int forward_impl(
 	E3Frame f = make_frame(P, D, M, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
 	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
 
-	char* gbuf = geometry_alloc(geometry_ctx, e3_geometry_bytes(P));
+	char* gbuf = ws ? ws->g : geometry_alloc(geometry_ctx, e3_geometry_bytes(P));
 	if (!gbuf) return E3_ERR_ALLOC_FAILED;
 	E3GeomState g = E3GeomState::carve(gbuf, P);
-	char* ibuf = image_alloc(image_ctx, e3_image_bytes(width, height));
+	char* ibuf = ws ? ws->i : image_alloc(image_ctx, e3_image_bytes(width, height));
 	if (!ibuf) return E3_ERR_ALLOC_FAILED;
 	E3ImageState im = E3ImageState::carve(ibuf, N, T);
 
@@ -160,25 +166,37 @@ static int forward_impl(
 	E3_STAGE(E3_STAGE_OFFSETS_SCAN, e3_exclusive_scan_u32(g.tiles_touched, order, g.offsets, (size_t)P, g.scan_tmp,
 		reinterpret_cast<uint32_t*>(g.flags), st));
 
-	int h_flags[2] = { 0, 0 };
-	E3_CHECK(cudaMemcpyAsync(h_flags, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-	E3_CHECK(cudaStreamSynchronize(st));        // the reference's blocking read of R (rasterizer_impl.cu:281)
-	if (h_flags[1]) return E3_ERR_PREFILTERED;
-	const int R = h_flags[0];
-	*num_rendered_host = R;
-
-	char* bbuf = binning_alloc(binning_ctx, e3_binning_bytes(R));
-	if (!bbuf) return E3_ERR_ALLOC_FAILED;
+	int R;
+	char* bbuf;
+	const uint32_t* n_dev = nullptr;
+	if (ws) {
+		// no host round trip: R stays on the device (flags[0]); everything downstream is launched for
+		// the caller's capacity and bounds itself by min(R, cap). The host copy of {R, prefiltered flag}
+		// lands in r_host[0..1] when the stream gets there.
+		E3_CHECK(cudaMemcpyAsync(ws->r_host, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+		R = (int)ws->cap;
+		bbuf = ws->b;
+		n_dev = reinterpret_cast<const uint32_t*>(g.flags);
+	} else {
+		int h_flags[2] = { 0, 0 };
+		E3_CHECK(cudaMemcpyAsync(h_flags, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+		E3_CHECK(cudaStreamSynchronize(st));        // the reference's blocking read of R (rasterizer_impl.cu:281)
+		if (h_flags[1]) return E3_ERR_PREFILTERED;
+		R = h_flags[0];
+		*num_rendered_host = R;
+		bbuf = binning_alloc(binning_ctx, e3_binning_bytes(R));
+		if (!bbuf) return E3_ERR_ALLOC_FAILED;
+	}
 	E3BinState b = E3BinState::carve(bbuf, (size_t)R);
 
 	// emit into the ping-pong slot from which the tile sort ends in slot 0, where backward looks
 	const int tile_bits = (int)higher_msb((uint32_t)T);
 	const int s0 = (R > 0) ? (e3_radix_passes(tile_bits) & 1) : 0;
-	E3_STAGE(E3_STAGE_EMIT, e3_launch_emit_instances(P, order, g.offsets, g.tiles_touched, g.rect, f.gx, b.tkey[s0], b.val[s0], st));
+	E3_STAGE(E3_STAGE_EMIT, e3_launch_emit_instances(P, order, g.offsets, g.tiles_touched, g.rect, f.gx, b.tkey[s0], b.val[s0], (uint32_t)R, st));
 	int bres = 0;
-	E3_STAGE(E3_STAGE_TILE_SORT, e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, tile_bits, b.sort_counts, b.scan_tmp, s0, &bres, st));
+	E3_STAGE(E3_STAGE_TILE_SORT, e3_radix_sort_pairs(b.tkey, b.val, (size_t)R, tile_bits, b.sort_counts, b.scan_tmp, s0, &bres, st, n_dev));
 	if (bres != 0) return E3_ERR_BAD_ARGUMENT;
-	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st));
+	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_ranges((size_t)R, b.tkey[0], im.ranges, T, st, n_dev));
 	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_order(im.ranges, (int)T, im.tile_order, st));
 	// single-channel raw mode blends against the luma of the background (written by the preprocess kernel)
 	const float* bg_used = (raw && channels == 1) ? reinterpret_cast<const float*>(g.flags) + 2 : background;
@@ -198,7 +216,7 @@ int e3_rasterize_forward(
 	float tan_fovx, float tan_fovy, int prefiltered,
 	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host)
 {
-	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, channels,
+	return forward_impl(nullptr, geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, channels,
 		background, width, height, means3D, shs, nullptr, false, colors_precomp, opacities, scales, scale_modifier, rotations,
 		cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, radii, debug, stream,
 		num_rendered_host);
@@ -218,10 +236,28 @@ int e3_rasterize_forward_raw(
 {
 	if (active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
 	if (P > 0 && (!features_dc || (active_sh_degree > 0 && !features_rest))) return E3_ERR_BAD_ARGUMENT;
-	return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, active_sh_degree, 16, channels,
+	return forward_impl(nullptr, geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, active_sh_degree, 16, channels,
 		background, width, height, xyz, features_dc, features_rest, true, nullptr, opacity_logits, log_scales, scale_modifier,
 		raw_rotations, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, 0, out_color, radii, debug, stream,
 		num_rendered_host);
+}
+
+int e3_rasterize_forward_raw_ws(
+	char* geometry_buffer, char* binning_buffer, size_t binning_capacity, char* image_buffer, int* num_rendered_host,
+	int P, int active_sh_degree, int channels,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy,
+	float* out_color, int* radii, int debug, void* stream)
+{
+	if (active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
+	if (P > 0 && (!features_dc || (active_sh_degree > 0 && !features_rest))) return E3_ERR_BAD_ARGUMENT;
+	WsMode ws = { geometry_buffer, binning_buffer, binning_capacity, image_buffer, num_rendered_host };
+	return forward_impl(&ws, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, P, active_sh_degree, 16, channels,
+		background, width, height, xyz, features_dc, features_rest, true, nullptr, opacity_logits, log_scales, scale_modifier,
+		raw_rotations, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, 0, out_color, radii, debug, stream, nullptr);
 }
 
 int e3_rasterize_backward(
@@ -261,7 +297,8 @@ int e3_rasterize_backward(
 	return 0;
 }
 
-int e3_rasterize_backward_raw(
+// phase bit 0: backward blend (into the packed accumulators); bit 1: backward preprocess (to the outputs)
+static int backward_raw_impl(int phase,
 	int P, int active_sh_degree, int channels, int R,
 	const float* background, int width, int height,
 	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
@@ -287,15 +324,35 @@ int e3_rasterize_backward_raw(
 	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
 	const float* bg_used = channels == 1 ? reinterpret_cast<const float*>(g.flags) + 2 : background;
-	if (R > 0) {
+	if (R > 0 && (phase & 1)) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
 		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib,
 			dL_dpix, g.acc, st));
 	}
-	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,
-		accumulate != 0, log_scales, raw_rotations, nullptr, viewmatrix, projmatrix, campos, g, d_mean2D, nullptr, d_opacity_logits,
-		nullptr, d_xyz, nullptr, d_features_dc, active_sh_degree > 0 ? d_features_rest : nullptr, d_log_scales, d_raw_rotations, st));
+	if (phase & 2)
+		E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,
+			accumulate != 0, log_scales, raw_rotations, nullptr, viewmatrix, projmatrix, campos, g, d_mean2D, nullptr, d_opacity_logits,
+			nullptr, d_xyz, nullptr, d_features_dc, active_sh_degree > 0 ? d_features_rest : nullptr, d_log_scales, d_raw_rotations, st));
 	return 0;
+}
+
+int e3_rasterize_backward_raw(
+	int P, int active_sh_degree, int channels, int R,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, int accumulate,
+	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
+	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
+	int debug, void* stream)
+{
+	return backward_raw_impl(3, P, active_sh_degree, channels, R, background, width, height, xyz, features_dc, features_rest,
+		opacity_logits, log_scales, scale_modifier, raw_rotations, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+		geometry_buffer, binning_buffer, image_buffer, dL_dpix, accumulate, d_xyz, d_features_dc, d_features_rest, d_opacity_logits,
+		d_log_scales, d_raw_rotations, d_mean2D, debug, stream);
 }
 
 int e3_event_loss(int width, int height, const float* image, const float* image_now, const float* image_next,
@@ -336,6 +393,86 @@ int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch
 	}
 	if (!in || !out || !scratch || scratch_bytes < e3_scan_scratch_bytes(n)) return E3_ERR_BAD_ARGUMENT;
 	E3_CHECK(e3_exclusive_scan_u32(in, nullptr, out, n, static_cast<uint32_t*>(scratch), total, (cudaStream_t)stream));
+	return 0;
+}
+
+// Two side streams and their fork/join events per device: the three views of an iteration are
+// independent until the loss and again until the gradient accumulation, and at event-camera
+// resolutions one view alone does not fill the 148 SMs (374 tiles at 346x260).
+struct ViewStreams { cudaStream_t side[2]; cudaEvent_t fork, join[2]; bool ok; };
+static ViewStreams g_view_streams[64];
+static std::mutex g_view_streams_mu;
+
+static cudaError_t view_streams(ViewStreams** out)
+{
+	int dev = 0;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) return e;
+	if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+	std::lock_guard<std::mutex> l(g_view_streams_mu);
+	ViewStreams& v = g_view_streams[dev];
+	if (!v.ok) {
+		for (int i = 0; i < 2; i++) {
+			if ((e = cudaStreamCreateWithFlags(&v.side[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+			if ((e = cudaEventCreateWithFlags(&v.join[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+		}
+		if ((e = cudaEventCreateWithFlags(&v.fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+		v.ok = true;
+	}
+	*out = &v;
+	return cudaSuccess;
+}
+
+int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
+{
+	if (!a) return E3_ERR_BAD_ARGUMENT;
+	if (a->views[1].channels != a->views[2].channels || a->views[0].channels != 3) return E3_ERR_BAD_ARGUMENT;
+	cudaStream_t main_st = (cudaStream_t)stream;
+	ViewStreams* vs = nullptr;
+	E3_CHECK(view_streams(&vs));
+	cudaStream_t sts[3] = { main_st, vs->side[0], vs->side[1] };
+	// ---- three forwards, one stream each ----
+	E3_CHECK(cudaEventRecord(vs->fork, main_st));
+	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
+	for (int k = 0; k < 3; k++) {
+		const e3_view& v = a->views[k];
+		int rc = e3_rasterize_forward_raw_ws(v.geometry_buffer, v.binning_buffer, (size_t)a->binning_capacity, v.image_buffer,
+			v.num_rendered_host, a->P, a->active_sh_degree, v.channels, a->background, a->width, a->height, a->xyz, a->features_dc,
+			a->features_rest, a->opacity_logits, a->log_scales, a->scale_modifier, a->raw_rotations, v.viewmatrix, v.projmatrix,
+			v.cam_pos, v.tan_fovx, v.tan_fovy, v.out_color, v.radii, 0, sts[k]);
+		if (rc) return rc;
+	}
+	for (int k = 1; k < 3; k++) {
+		E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
+		E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
+	}
+	if (a->forwards_done_event) E3_CHECK(cudaEventRecord((cudaEvent_t)a->forwards_done_event, main_st));
+	if (a->P == 0) return 0;
+	if (a->wait_before_loss_event) E3_CHECK(cudaStreamWaitEvent(main_st, (cudaEvent_t)a->wait_before_loss_event, 0));
+	int rc = e3_event_loss(a->width, a->height, a->views[0].out_color, a->views[1].out_color, a->views[2].out_color, a->gt_now,
+		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, 1.0f, a->views[1].channels, a->loss_scratch, 64,
+		a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, main_st);
+	if (rc) return rc;
+	// ---- three backward blends concurrently, then the three gradient accumulations in order ----
+	E3_CHECK(cudaEventRecord(vs->fork, main_st));
+	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
+	for (int phase = 1; phase <= 2; phase++) {
+		for (int k = 0; k < 3; k++) {
+			const e3_view& v = a->views[k];
+			rc = backward_raw_impl(phase, a->P, a->active_sh_degree, v.channels, (int)a->binning_capacity, a->background, a->width,
+				a->height, a->xyz, a->features_dc, a->features_rest, a->opacity_logits, a->log_scales, a->scale_modifier,
+				a->raw_rotations, v.viewmatrix, v.projmatrix, v.cam_pos, v.tan_fovx, v.tan_fovy, v.radii, v.geometry_buffer,
+				v.binning_buffer, v.image_buffer, v.seed, (k > 0 || a->accumulate) ? 1 : 0, a->d_xyz, a->d_features_dc,
+				a->d_features_rest, a->d_opacity_logits, a->d_log_scales, a->d_raw_rotations, k == 0 ? a->d_mean2D : nullptr, 0,
+				phase == 1 ? sts[k] : main_st);
+			if (rc) return rc;
+		}
+		if (phase == 1)
+			for (int k = 1; k < 3; k++) {
+				E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
+				E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
+			}
+	}
 	return 0;
 }
 

@@ -117,9 +117,12 @@ __global__ void __launch_bounds__(E3_SCAN_THREADS) scan_down_kernel(const uint32
 
 struct RadixPlan { int npass; int shift[4]; int bits[4]; };
 
+// n_dev (optional): the element count lives on the device (no host round trip); `n` is then the
+// capacity the launch was sized for and the effective count is min(*n_dev, n).
 __global__ void __launch_bounds__(256) radix_hist_all_kernel(const uint32_t* __restrict__ keys, size_t n, RadixPlan plan,
-	uint32_t* __restrict__ ghist)
+	uint32_t* __restrict__ ghist, const uint32_t* __restrict__ n_dev)
 {
+	if (n_dev) n = min(n, (size_t)*n_dev);
 	__shared__ uint32_t hist[4][256];
 	for (int i = threadIdx.x; i < 4 * 256; i += 256) (&hist[0][0])[i] = 0;
 	__syncthreads();
@@ -139,8 +142,9 @@ __global__ void __launch_bounds__(256) radix_hist_all_kernel(const uint32_t* __r
 __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
 	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
 	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist, volatile uint32_t* lookback,
-	uint32_t* __restrict__ tile_counter)
+	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev)
 {
+	if (n_dev) n = min(n, (size_t)*n_dev);
 	__shared__ uint32_t wcnt[8][256];
 	__shared__ uint32_t s_keys[E3_SORT_TILE];
 	__shared__ uint32_t s_vals[E3_SORT_TILE];
@@ -155,6 +159,7 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 	const uint32_t lt = (1u << lane) - 1u;
 	const size_t tstart = (size_t)tile * E3_SORT_TILE;
+	if (tstart >= n) return;       // launch sized for a capacity: tiles past the data have nothing to do (block-uniform)
 	const size_t wstart = tstart + (size_t)w * (32 * E3_SORT_ITEMS);
 	const uint32_t tcount = (uint32_t)min((size_t)E3_SORT_TILE, n - tstart);
 	uint32_t key[E3_SORT_ITEMS], val[E3_SORT_ITEMS];
@@ -242,8 +247,10 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 // splat does not stall 31 idle lanes (the reference's serial inner loop does).
 __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32_t* __restrict__ order,
 	const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ tiles_touched,
-	const uint2* __restrict__ rect, int gx, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals)
+	const uint2* __restrict__ rect, int gx, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals, uint32_t cap)
 {
+	// cap: capacity of tkeys / vals. With a host-known R it equals R; on the no-sync path it is the
+	// caller's estimate and instances beyond it are dropped (the host detects R > cap and redoes the step).
 	const int k = blockIdx.x * blockDim.x + threadIdx.x;
 	const int lane = threadIdx.x & 31;
 	uint32_t idx = 0, tt = 0, off = 0;
@@ -259,7 +266,7 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
 		uint32_t o = off;
 		const uint32_t y1 = rc.y >> 16;
 		for (uint32_t y = y0; y < y1; y++)
-			for (uint32_t x = x0; x < x1; x++) { tkeys[o] = y * gx + x; vals[o] = idx; o++; }
+			for (uint32_t x = x0; x < x1; x++) { if (o < cap) { tkeys[o] = y * gx + x; vals[o] = idx; } o++; }
 	}
 	uint32_t big = __ballot_sync(E3_FULL, tt > 32);
 	while (big) {
@@ -270,16 +277,19 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
 		const uint32_t b_y0 = __shfl_sync(E3_FULL, y0, src), b_w = __shfl_sync(E3_FULL, wdt, src);
 		for (uint32_t i = lane; i < b_tt; i += 32) {
 			const uint32_t yy = i / b_w, xx = i - yy * b_w;
-			tkeys[b_off + i] = (b_y0 + yy) * gx + (b_x0 + xx);
-			vals[b_off + i] = b_idx;
+			if (b_off + i < cap) {
+				tkeys[b_off + i] = (b_y0 + yy) * gx + (b_x0 + xx);
+				vals[b_off + i] = b_idx;
+			}
 		}
 	}
 }
 
 // identifyTileRanges, rasterizer_impl.cu:116-138, on 32-bit tile ids
 __global__ void __launch_bounds__(256) tile_ranges_kernel(size_t L, const uint32_t* __restrict__ tkeys,
-	uint2* __restrict__ ranges)
+	uint2* __restrict__ ranges, const uint32_t* __restrict__ n_dev)
 {
+	if (n_dev) L = min(L, (size_t)*n_dev);
 	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= L) return;
 	const uint32_t cur = tkeys[idx];
@@ -309,7 +319,7 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 }
 
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st)
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev)
 {
 	(void)scan_tmp;
 	int cur = start_buf;
@@ -332,10 +342,10 @@ cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, 
 		cudaError_t e = cudaMemsetAsync(counts, 0, e3_sort_scratch_words(n) * sizeof(uint32_t), st);
 		if (e != cudaSuccess) return e;
 		const unsigned hgrid = (unsigned)(nblk < 1184 ? nblk : 1184);
-		radix_hist_all_kernel<<<hgrid, 256, 0, st>>>(keys[cur], n, plan, ghist);
+		radix_hist_all_kernel<<<hgrid, 256, 0, st>>>(keys[cur], n, plan, ghist, n_dev);
 		for (int p = 0; p < plan.npass; p++) {
 			radix_onesweep_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * nblk * 256, tile_counter + p);
+				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * nblk * 256, tile_counter + p, n_dev);
 			cur ^= 1;
 		}
 		g_e3_launches += 1 + plan.npass;
@@ -345,18 +355,18 @@ cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, 
 }
 
 cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_t* offsets,
-	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals,
+	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals, uint32_t cap,
 	cudaStream_t st)
 {
-	emit_instances_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tiles_touched, rect, gx, tkeys, vals);
+	emit_instances_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tiles_touched, rect, gx, tkeys, vals, cap);
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }
 
-cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges, size_t T, cudaStream_t st)
+cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges, size_t T, cudaStream_t st, const uint32_t* n_dev)
 {
 	cudaError_t e = cudaMemsetAsync(ranges, 0, T * sizeof(uint2), st);
 	if (e != cudaSuccess) return e;
-	if (R > 0) { tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges); g_e3_launches += 1; }
+	if (R > 0) { tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges, n_dev); g_e3_launches += 1; }
 	return cudaGetLastError();
 }

@@ -147,12 +147,12 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 // the result. e3_radix_passes() tells how many passes (buffer flips) that takes.
 static inline int e3_radix_passes(int end_bit) { return (end_bit + 7) / 8; }
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st);
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev = nullptr);
 cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_t* offsets,
-	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals,
+	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals, uint32_t cap,
 	cudaStream_t st);
 cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges, size_t T,
-	cudaStream_t st);
+	cudaStream_t st, const uint32_t* n_dev = nullptr);
 
 cudaError_t e3_launch_tile_order(const uint2* ranges, int T, uint32_t* order, cudaStream_t st);
 cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,

@@ -24,7 +24,72 @@ class RenderState:
     __slots__ = ("R", "color", "radii", "geom", "binning", "img", "cam", "tanfovx", "tanfovy", "channels")
 
 
-def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False, channels=3):
+class Workspace:
+    """Caller-owned state buffers of the no-sync path (e3_rasterize_forward_raw_ws): one slot per
+    render that is alive at the same time (3 per event iteration), kept for the whole run. The
+    binning buffers hold `cap` instances; num_rendered of every forward arrives asynchronously in
+    pinned host memory and is checked against `cap` once per iteration (check())."""
+
+    def __init__(self, P, W, H, device, cap, slots=3):
+        L = _lib.lib()
+        self.P, self.W, self.H, self.device, self.slots = P, W, H, device, slots
+        u8 = dict(dtype=torch.uint8, device=device)
+        self.geom = [torch.empty(L.e3_geometry_bytes(P), **u8) for _ in range(slots)]
+        self.img = [torch.empty(L.e3_image_bytes(W, H), **u8) for _ in range(slots)]
+        self.r_host = torch.zeros(slots, 2, dtype=torch.int32).pin_memory()
+        self.events = [torch.cuda.Event() for _ in range(slots)]
+        self.used = [False] * slots
+        # single-call iteration (e3_event_iteration): seeds, loss scratch, one event after the forwards
+        self.seeds = {}
+        self.loss_scratch = torch.empty(8, dtype=torch.float64, device=device)
+        self.fw_event = torch.cuda.Event()
+        with torch.cuda.device(device):
+            self.fw_event.record(torch.cuda.current_stream(device))      # creates the underlying cudaEvent_t
+        self.args = _lib.EventIterationArgs()
+        self.pending_single = False
+        self.resize(cap)
+
+    def resize(self, cap):
+        L = _lib.lib()
+        self.cap = int(max(cap, 4096))
+        self.bin = [torch.empty(L.e3_binning_bytes(self.cap), dtype=torch.uint8, device=self.device) for _ in range(self.slots)]
+
+    def seed(self, k, channels):
+        t = self.seeds.get((k, channels))
+        if t is None:
+            t = self.seeds[(k, channels)] = torch.empty(channels, self.H, self.W, dtype=torch.float32, device=self.device)
+        return t
+
+    def matches(self, P, W, H, device):
+        return (self.P, self.W, self.H, self.device) == (P, W, H, device)
+
+    def check(self):
+        """Wait for the R read-backs of the slots used since the last check (they precede the loss
+        and backward kernels in the stream, so this does not drain the pipeline). Returns the
+        measured R per slot; raises Overflow after enlarging the buffers if one exceeded cap."""
+        Rs, worst = [], 0
+        if self.pending_single:
+            self.fw_event.synchronize()
+            self.pending_single = False
+            Rs = [int(self.r_host[k, 0]) for k in range(3)]
+        for k in range(self.slots):
+            if self.used[k]:
+                self.events[k].synchronize()
+                Rs.append(int(self.r_host[k, 0]))
+                self.used[k] = False
+        worst = max(Rs) if Rs else 0
+        if worst > self.cap:
+            self.resize(int(worst * 1.5))
+            raise Workspace.Overflow(worst)
+        return Rs
+
+    class Overflow(RuntimeError):
+        pass
+
+
+def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False, channels=3, ws=None, slot=0):
+    if ws is not None:
+        return _forward_raw_ws(pc, cam, bg, scaling_modifier, debug, channels, ws, slot)
     L = _lib.lib()
     xyz = pc._xyz
     P = xyz.shape[0]
@@ -56,6 +121,34 @@ def _forward_raw(pc, cam, bg, scaling_modifier=1.0, debug=False, channels=3):
     _slots.clear()
     _lib.check(code)
     st.R = R.value
+    return st
+
+
+def _forward_raw_ws(pc, cam, bg, scaling_modifier, debug, channels, ws, slot):
+    L = _lib.lib()
+    xyz = pc._xyz
+    P = xyz.shape[0]
+    dev = xyz.device
+    H, W = int(cam.image_height), int(cam.image_width)
+    st = RenderState()
+    st.cam, st.channels = cam, channels
+    st.tanfovx = math.tan(cam.FoVx * 0.5)
+    st.tanfovy = math.tan(cam.FoVy * 0.5)
+    st.radii = torch.empty(P, dtype=torch.int32, device=dev)
+    st.color = torch.empty(channels, H, W, dtype=torch.float32, device=dev)
+    st.geom, st.binning, st.img, st.R = ws.geom[slot], ws.bin[slot], ws.img[slot], ws.cap
+    stream = torch.cuda.current_stream(dev)
+    with torch.cuda.device(dev):
+        code = L.e3_rasterize_forward_raw_ws(
+            st.geom.data_ptr(), st.binning.data_ptr(), ws.cap, st.img.data_ptr(), ws.r_host[slot].data_ptr(), P,
+            int(pc.active_sh_degree), channels, bg.data_ptr(), W, H, xyz.data_ptr(), pc._features_dc.data_ptr(),
+            pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(), float(scaling_modifier),
+            pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(), cam.full_proj_transform.data_ptr(),
+            cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.color.data_ptr(), st.radii.data_ptr(), int(debug),
+            stream.cuda_stream)
+    _lib.check(code)
+    ws.events[slot].record(stream)
+    ws.used[slot] = True
     return st
 
 
@@ -133,7 +226,7 @@ def same_view(cam_a, cam_b):
 
 
 def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
-                             dedupe_views=False, gray_event_views=True, gt_ready=None, accumulate=False):
+                             dedupe_views=False, gray_event_views=True, gt_ready=None, accumulate=False, no_sync=True):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
@@ -152,6 +245,9 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     gt_ready: optional torch.cuda.Event recorded after the GT frames were copied to the device on
     another stream; the loss waits for it, so the host-to-device copy overlaps the three renders.
 
+    no_sync: after the first call (which reads num_rendered back like the reference and sizes a
+    persistent Workspace from it) no forward blocks the host any more; see Workspace.
+
     accumulate: add this view-pair's gradients to the ones the previous call left (several pairs per
     optimizer step, e.g. BASELINE config c5 with 64 pairs per step); the returned loss is this
     pair's. The caller divides by the number of pairs (or lets parallel.allreduce_flat average over
@@ -166,7 +262,14 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("event_3dgs_b200.fused: tensors must be contiguous float32 CUDA tensors")
     ec = 1 if gray_event_views else 3
-    sts = [_forward_raw(pc, cam_train, bg), _forward_raw(pc, cam_now, bg, channels=ec), _forward_raw(pc, cam_next, bg, channels=ec)]
+    ws = _workspace_for(pc, cam_train) if no_sync and pc._xyz.shape[0] > 0 else None
+    if ws is not None:
+        return _event_iteration_single_call(pc, (cam_train, cam_now, cam_next), gt, c, bg, deblur, return_pkg, ec, gt_ready,
+                                            accumulate, ws)
+    sts = [_forward_raw(pc, cam_train, bg, ws=ws, slot=0), _forward_raw(pc, cam_now, bg, channels=ec, ws=ws, slot=1),
+           _forward_raw(pc, cam_next, bg, channels=ec, ws=ws, slot=2)]
+    if ws is None and no_sync and pc._xyz.shape[0] > 0:
+        _remember_workspace(pc, cam_train, max(s.R for s in sts))
     if gt_ready is not None:
         torch.cuda.current_stream(pc._xyz.device).wait_event(gt_ready)
     out, seeds = event_loss_and_seeds(sts[0].color, sts[1].color, sts[2].color, gt, c, deblur)
@@ -176,6 +279,17 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     _backward_raw(pc, sts[0], bg, seeds["image"], grads, accumulate, d_mean2D)
     _backward_raw(pc, sts[1], bg, seeds["image_now"], grads, True)
     _backward_raw(pc, sts[2], bg, seeds["image_next"], grads, True)
+    if ws is not None:
+        try:
+            Rs = ws.check()
+        except Workspace.Overflow:
+            # more instances than the workspace was sized for: it has been enlarged, redo the step
+            if accumulate:
+                raise RuntimeError("event_3dgs_b200.fused: workspace overflow during an accumulating step; repeat the optimizer step")
+            return event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur, return_pkg, dedupe_views,
+                                            gray_event_views, None, accumulate, no_sync)
+        for s_, r_ in zip(sts, Rs):
+            s_.R = r_
     if accumulate:
         grads["c"].add_(out[1:2])
         return out[0]
@@ -194,6 +308,88 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
                "radii": sts[0].radii, "num_rendered": [s.R for s in sts], "loss_terms": out}
         return loss, pkg
     return loss
+
+
+def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, gt_ready, accumulate, ws):
+    """The whole iteration through ONE C call (e3_event_iteration) on the persistent workspace: no host
+    synchronisation, no per-render Python work. Falls back to itself once if the workspace overflowed."""
+    L = _lib.lib()
+    dev = pc._xyz.device
+    P, D = pc._xyz.shape[0], int(pc.active_sh_degree)
+    H, W = ws.H, ws.W
+    blur = gt["blurry"] if deblur else None
+    frames = [gt["event_now"], gt["event_next"], gt["intensity"]] + ([blur] if blur is not None else [])
+    u8 = frames[0].dtype == torch.uint8
+    for f in frames:
+        if f.dtype != (torch.uint8 if u8 else torch.float32) or not f.is_contiguous() or tuple(f.shape) != (3, H, W) or f.device != dev:
+            raise RuntimeError("event_3dgs_b200.fused: GT frames must be contiguous [3,H,W] on the model's device, all float32 or all uint8")
+    grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D)
+    chans = (3, ec, ec)
+    colors = [torch.empty(ch, H, W, dtype=torch.float32, device=dev) for ch in chans]
+    radii = [torch.empty(P, dtype=torch.int32, device=dev) for _ in range(3)]
+    out = torch.empty(5, dtype=torch.float32, device=dev)
+    d_mean2D = None if accumulate else torch.empty_like(pc._xyz)
+    a = ws.args
+    a.P, a.active_sh_degree, a.width, a.height = P, D, W, H
+    a.binning_capacity, a.scale_modifier, a.accumulate = ws.cap, 1.0, int(bool(accumulate))
+    a.background = bg.data_ptr()
+    a.xyz, a.features_dc, a.features_rest = pc._xyz.data_ptr(), pc._features_dc.data_ptr(), pc._features_rest.data_ptr()
+    a.opacity_logits, a.log_scales, a.raw_rotations = pc._opacity.data_ptr(), pc._scaling.data_ptr(), pc._rotation.data_ptr()
+    a.d_xyz, a.d_features_dc = grads["xyz"].data_ptr(), grads["features_dc"].data_ptr()
+    a.d_features_rest = grads["features_rest"].data_ptr() if D > 0 else None
+    a.d_opacity_logits, a.d_log_scales, a.d_raw_rotations = grads["opacity"].data_ptr(), grads["scaling"].data_ptr(), grads["rotation"].data_ptr()
+    a.d_mean2D = None if d_mean2D is None else d_mean2D.data_ptr()
+    for k, cam in enumerate(cams3):
+        v = a.views[k]
+        v.viewmatrix, v.projmatrix, v.cam_pos = cam.world_view_transform.data_ptr(), cam.full_proj_transform.data_ptr(), cam.camera_center.data_ptr()
+        v.tan_fovx, v.tan_fovy, v.channels = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), chans[k]
+        v.geometry_buffer, v.binning_buffer, v.image_buffer = ws.geom[k].data_ptr(), ws.bin[k].data_ptr(), ws.img[k].data_ptr()
+        v.out_color, v.radii, v.seed = colors[k].data_ptr(), radii[k].data_ptr(), ws.seed(k, chans[k]).data_ptr()
+        v.num_rendered_host = ws.r_host[k].data_ptr()
+    a.gt_now, a.gt_next, a.gt_intensity = gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr()
+    a.gt_blur = None if blur is None else blur.data_ptr()
+    a.gt_is_u8, a.c, a.out5, a.loss_scratch = int(u8), c.data_ptr(), out.data_ptr(), ws.loss_scratch.data_ptr()
+    a.forwards_done_event = ws.fw_event.cuda_event
+    stream = torch.cuda.current_stream(dev)
+    a.wait_before_loss_event = gt_ready.cuda_event if gt_ready is not None else None
+    with torch.cuda.device(dev):
+        code = L.e3_event_iteration(ctypes.byref(a), stream.cuda_stream)
+    _lib.check(code)
+    ws.pending_single = True
+    try:
+        Rs = ws.check()
+    except Workspace.Overflow:
+        if accumulate:
+            raise RuntimeError("event_3dgs_b200.fused: workspace overflow during an accumulating step; repeat the optimizer step")
+        return _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, None, accumulate, ws)
+    if accumulate:
+        grads["c"].add_(out[1:2])
+        return out[0]
+    pc._xyz.grad = grads["xyz"]
+    pc._features_dc.grad = grads["features_dc"]
+    pc._features_rest.grad = grads["features_rest"]
+    pc._opacity.grad = grads["opacity"]
+    pc._scaling.grad = grads["scaling"]
+    pc._rotation.grad = grads["rotation"]
+    _finish_c_grad(c, grads, out)
+    if return_pkg:
+        vsp = torch.zeros_like(pc._xyz)
+        vsp.grad = d_mean2D
+        return out[0], {"render": colors[0], "viewspace_points": vsp, "visibility_filter": radii[0] > 0, "radii": radii[0],
+                        "num_rendered": Rs, "loss_terms": out}
+    return out[0]
+
+
+def _workspace_for(pc, cam):
+    ws = getattr(pc, "_e3_ws", None)
+    if ws is not None and ws.matches(pc._xyz.shape[0], int(cam.image_width), int(cam.image_height), pc._xyz.device):
+        return ws
+    return None
+
+
+def _remember_workspace(pc, cam, r_max):
+    """First (synchronous) step done: size the persistent workspace from the measured num_rendered."""
+    pc._e3_ws = Workspace(pc._xyz.shape[0], int(cam.image_width), int(cam.image_height), pc._xyz.device, int(r_max * 1.3) + 4096)
 
 
 def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg, gt_ready=None):

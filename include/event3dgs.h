@@ -150,6 +150,29 @@ E3_API int e3_rasterize_forward_raw(
 	float tan_fovx, float tan_fovy,
 	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host);
 
+/* e3_rasterize_forward_raw without the host round trip. The reference blocks the host in every
+ * forward to read num_rendered and size the binning buffer (cuda_rasterizer/rasterizer_impl.cu:
+ * 281-285); at event-camera resolutions (346x260) that stall and the launch gaps around it cost more
+ * than the kernels. Here the caller owns all three buffers for the whole training run:
+ * geometry_buffer >= e3_geometry_bytes(P), image_buffer >= e3_image_bytes(W, H), binning_buffer >=
+ * e3_binning_bytes(binning_capacity) with binning_capacity an estimate of num_rendered (e.g. 1.3x
+ * the largest value seen). R stays on the device; every later kernel is launched for the capacity
+ * and bounds itself by min(R, capacity). {R, prefiltered flag} are copied asynchronously to
+ * num_rendered_host[0..1] (pinned host memory): once the stream has passed that copy the caller
+ * checks R <= binning_capacity and, if not, enlarges the buffer and repeats the step (the results of
+ * an overflowed call are defined but incomplete). For the backward pass hand
+ * e3_rasterize_backward_raw the same buffers and binning_capacity as its R. */
+E3_API int e3_rasterize_forward_raw_ws(
+	char* geometry_buffer, char* binning_buffer, size_t binning_capacity, char* image_buffer,
+	int* num_rendered_host,
+	int P, int active_sh_degree, int channels,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy,
+	float* out_color, int* radii, int debug, void* stream);
+
 /* Backward of e3_rasterize_forward_raw down to the leaf parameters (what loss.backward() produces
  * in the reference through _RasterizeGaussians.backward and the autograd graph of render()).
  * accumulate = 0: every row of the outputs is written (zeros for culled Gaussians);
@@ -220,6 +243,53 @@ E3_API size_t e3_l1_ssim_scratch_bytes(int width, int height, int gray);
 E3_API int e3_l1_ssim_loss(int width, int height, int gray, const float* image, const void* gt,
 	int gt_is_u8, float lambda_dssim, float upstream, void* scratch, size_t scratch_bytes,
 	float* d_image, float* out3, void* stream);
+
+/* One whole event training iteration in one call: the three renders of train.py:144,159-162, the
+ * event loss of :165-203 and loss.backward() (:211) down to the leaf parameters, enqueued without
+ * any host synchronisation (e3_rasterize_forward_raw_ws x3, e3_event_loss, e3_rasterize_backward_raw
+ * x3). Exists because at event-camera resolutions the ~75 kernels of an iteration are shorter than
+ * the host work of seven separate binding calls. Everything is caller-owned and may be reused
+ * from call to call, which also makes the call sequence fixed (capturable by the caller).
+ * views[0] = intensity view (3 channels), views[1], views[2] = event views `index`, `index+1`
+ * (channels 1 = luma, or 3). seed buffers are [channels,H,W]. d_* receive the SUM of the three
+ * backward passes (overwritten, or added to when accumulate != 0); d_mean2D (optional) is the
+ * screen-space gradient of views[0]. out5 as in e3_event_loss. After the stream has passed the
+ * read-backs, check views[k].num_rendered_host[0] <= binning_capacity (see
+ * e3_rasterize_forward_raw_ws). */
+typedef struct e3_view {
+	const float* viewmatrix;
+	const float* projmatrix;
+	const float* cam_pos;
+	float tan_fovx, tan_fovy;
+	int channels;
+	char* geometry_buffer;
+	char* binning_buffer;
+	char* image_buffer;
+	float* out_color;
+	int* radii;
+	float* seed;
+	int* num_rendered_host;
+} e3_view;
+typedef struct e3_event_iteration_args {
+	int P, active_sh_degree, width, height;
+	unsigned long long binning_capacity;
+	float scale_modifier;
+	int accumulate;
+	const float* background;
+	const float *xyz, *features_dc, *features_rest, *opacity_logits, *log_scales, *raw_rotations;
+	float *d_xyz, *d_features_dc, *d_features_rest, *d_opacity_logits, *d_log_scales, *d_raw_rotations, *d_mean2D;
+	e3_view views[3];
+	const void *gt_now, *gt_next, *gt_intensity, *gt_blur;
+	int gt_is_u8;
+	const float* c;
+	float* out5;
+	void* loss_scratch;          /* >= 64 bytes, 8-byte aligned */
+	void* wait_before_loss_event;/* optional cudaEvent_t the stream waits for right before the loss kernels (e.g. the
+	                                upload of the GT frames on another stream, which then overlaps the renders) */
+	void* forwards_done_event;   /* optional cudaEvent_t, recorded after the third forward: waiting on it
+	                                makes the three num_rendered read-backs visible without draining the stream */
+} e3_event_iteration_args;
+E3_API int e3_event_iteration(const e3_event_iteration_args* args_host, void* stream);
 
 /* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
  * rasterizer_impl.cu:54-66,141-153): present[i] = view-space z > 0.2. present is uint8[P]. */

@@ -246,3 +246,30 @@ def test_accumulate_over_view_pairs(cuda_dev):
     fused.event_iteration_backward(pc, cams[4], cams[4], cams[5], gt, c, bg, accumulate=True)
     for p, a, b in zip(leaves, g1, g2):
         assert rel_err(p.grad.cpu().numpy(), (a + b).cpu().numpy(), 1e-20) < 1e-4
+
+
+def test_no_sync_workspace_path_and_overflow_recovery(cuda_dev):
+    from event_3dgs_b200 import fused
+    pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, 0, False)
+    leaves = pc.leaves() + [c]
+    la, pa = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True, no_sync=False)
+    ga = [p.grad.clone() for p in leaves]
+    img_a = pa["render"].clone()
+    assert getattr(pc, "_e3_ws", None) is None
+    # first no_sync call still synchronises (it sizes the workspace), the second one does not
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg)
+    ws = pc._e3_ws
+    assert ws is not None and ws.cap >= max(pa["num_rendered"])
+    lb, pb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True)
+    assert pb["num_rendered"] == pa["num_rendered"]
+    assert torch.equal(pb["render"], img_a) and torch.equal(pb["radii"], pa["radii"])
+    assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
+    for p, a in zip(leaves, ga):
+        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    # too small a workspace: the step notices, enlarges it and repeats itself
+    ws.resize(4096)
+    lc, pc_pkg = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True)
+    assert pc._e3_ws.cap >= max(pa["num_rendered"])
+    assert torch.equal(pc_pkg["render"], img_a)
+    for p, a in zip(leaves, ga):
+        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
