@@ -59,6 +59,13 @@ class AdamGroup(ctypes.Structure):
                 ("exp_avg_sq", ctypes.c_void_p), ("n", ctypes.c_ulonglong), ("lr", ctypes.c_float), ("eps", ctypes.c_float)]
 
 
+class DensifyArray(ctypes.Structure):
+    """e3_densify_array of include/event3dgs.h."""
+    _fields_ = [("src", ctypes.c_void_p), ("dst", ctypes.c_void_p), ("exp_avg_src", ctypes.c_void_p),
+                ("exp_avg_dst", ctypes.c_void_p), ("exp_avg_sq_src", ctypes.c_void_p), ("exp_avg_sq_dst", ctypes.c_void_p),
+                ("width", ctypes.c_int), ("kind", ctypes.c_int)]
+
+
 class View(ctypes.Structure):
     """e3_view of include/event3dgs.h."""
     _fields_ = [("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p), ("cam_pos", ctypes.c_void_p),
@@ -86,6 +93,11 @@ class EventIterationArgs(ctypes.Structure):
 
 SIGNATURES["e3_event_iteration"] = (_i, [ctypes.POINTER(EventIterationArgs), _vp])
 SIGNATURES["e3_adam_step"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, _vp])
+SIGNATURES["e3_densification_stats"] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp])
+SIGNATURES["e3_densify_scratch_bytes"] = (_sz, [_i])
+SIGNATURES["e3_densify_plan"] = (_i, [_i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _i, _vp, _sz, _vp, _vp])
+SIGNATURES["e3_densify_apply"] = (_i, [_i, _i, _i, ctypes.POINTER(DensifyArray), _i, _vp, _vp, _vp, _i, _vp, _sz, _vp])
+SIGNATURES["e3_reset_opacity"] = (_i, [_i, _vp, _vp, _vp, _f, _vp])
 
 _lib = None
 

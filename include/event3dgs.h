@@ -230,6 +230,64 @@ typedef struct e3_adam_group {
 E3_API int e3_adam_step(const e3_adam_group* groups_host, int num_groups, int step, double beta1,
 	double beta2, void* stream);
 
+/* Densification statistics of one iteration (train.py:317-320, scene/gaussian_model.py:405-407),
+ * one launch: for every Gaussian with radii > 0 (the visibility filter of the first render)
+ *   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |d_mean2D[:, :2]|; denom += 1.
+ * d_mean2D is the [P,3] screen-space gradient (viewspace_points.grad). */
+E3_API int e3_densification_stats(int P, const int* radii, const float* d_mean2D, float* max_radii2D,
+	float* xyz_gradient_accum, float* denom, void* stream);
+
+/* Adaptive density control, replacing GaussianModel.densify_and_prune (scene/gaussian_model.py:
+ * 389-403) together with the tensor / optimizer-state surgery beneath it (densify_and_clone
+ * :374-387, densify_and_split :349-372, densification_postfix :329-347, cat_tensors_to_optimizer
+ * :307-327, prune_points :291-305, _prune_optimizer :273-289). Two calls, because the new row count
+ * is only known after the first and the caller owns all memory:
+ *
+ *  e3_densify_plan   evaluates the clone / split / prune criteria on the P current rows and builds
+ *                    the row map in `scratch` (e3_densify_scratch_bytes(P) bytes of device memory).
+ *                    counts (device, 8 ints): [0] kept originals, [1] kept clones, [2] kept split
+ *                    children per draw, [3] split selections, [4] new row count P_new.
+ *                    dense_extent = percent_dense * scene_extent, rounded to float; the limit
+ *                    big_world_extent = 0.1 * scene_extent applies only when the reference passes a
+ *                    max_screen_size (train.py:323), pass a negative value otherwise. split_n is the
+ *                    reference's N (only its default 2 is supported, else E3_ERR_UNSUPPORTED).
+ *  e3_densify_apply  after the caller has read counts and allocated P_new-row outputs: ONE gather
+ *                    launch over all arrays. Output order = the reference's: kept originals, kept
+ *                    clones, kept children of the 1st draw, of the 2nd draw, each in source order.
+ *                    kind 0: rows copied. kind 1 (xyz, width 3): children get
+ *                    xyz + R(rotation) (exp(scaling) * z). kind 2 (scaling, width 3): children get
+ *                    log(exp(s) / (0.8 * split_n)). normals = the standard-normal draws z
+ *                    [split_n * counts[3], 3] in the reference's order (row c * counts[3] + rank of
+ *                    the selected Gaussian), i.e. what torch.normal(mean=0, std=stds) scales
+ *                    (gaussian_model.py:358-360). exp_avg / exp_avg_sq (optional): moments follow
+ *                    kept originals, new rows get zeros. rotation / scaling = the CURRENT (source)
+ *                    [P,4] / [P,3] raw parameters.
+ * The caller zeroes xyz_gradient_accum, denom, max_radii2D at the new size (gaussian_model.py:345-347). */
+#define E3_DENSIFY_MAX_ARRAYS 8
+typedef struct e3_densify_array {
+	const float* src;             /* [P, width] */
+	float* dst;                   /* [P_new, width] */
+	const float* exp_avg_src;     /* optional */
+	float* exp_avg_dst;
+	const float* exp_avg_sq_src;  /* optional */
+	float* exp_avg_sq_dst;
+	int width;
+	int kind;
+} e3_densify_array;
+E3_API size_t e3_densify_scratch_bytes(int P);
+E3_API int e3_densify_plan(int P, const float* xyz_gradient_accum, const float* denom, const float* scaling,
+	const float* opacity, float max_grad, float dense_extent, float min_opacity, float big_world_extent,
+	int split_n, void* scratch, size_t scratch_bytes, int* counts, void* stream);
+E3_API int e3_densify_apply(int P, int P_new, int num_split_selected, const e3_densify_array* arrays_host,
+	int num_arrays, const float* rotation, const float* scaling, const float* normals, int split_n,
+	const void* scratch, size_t scratch_bytes, void* stream);
+
+/* GaussianModel.reset_opacity (scene/gaussian_model.py:210-213, train.py:326-327), in place:
+ * opacity = inverse_sigmoid(min(sigmoid(opacity), max_opacity)) with max_opacity = 0.01, and the
+ * two Adam moments of the opacity group (optional) zeroed as replace_tensor_to_optimizer does. */
+E3_API int e3_reset_opacity(int P, float* opacity, float* exp_avg, float* exp_avg_sq, float max_opacity,
+	void* stream);
+
 /* L1 + SSIM loss of the two non-event training branches, value and backward seed:
  * loss = (1 - lambda_dssim) * L1 + lambda_dssim * (1 - SSIM), with the 11x11 Gaussian-window SSIM
  * of utils/loss_utils.py:359-418 (sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2).
