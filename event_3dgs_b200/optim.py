@@ -15,6 +15,25 @@ class FusedAdam(torch.optim.Optimizer):
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
 
+    def moments_are_zero(self, p):
+        """True while p has only ever been advanced by advance_without_update (or never stepped)."""
+        st = self.state.get(p, None)
+        return st is None or len(st) == 0 or bool(st.get("_moments_zero", False))
+
+    @torch.no_grad()
+    def advance_without_update(self, p):
+        """For a parameter whose gradient is identically zero and whose moments are zero: the Adam
+        update is the identity (m = v = 0, p -= lr * 0 / (0 + eps)); only the step counter moves."""
+        if not self.moments_are_zero(p):
+            raise RuntimeError("advance_without_update: the moments of this parameter are not zero")
+        st = self.state[p]
+        if len(st) == 0:
+            st["step"] = 0
+            st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        st["_moments_zero"] = True
+        st["step"] = int(st["step"]) + 1
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -36,6 +55,7 @@ class FusedAdam(torch.optim.Optimizer):
                     st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                     st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                 st["step"] = int(st["step"]) + 1
+                st.pop("_moments_zero", None)
                 key = (st["step"], float(b1), float(b2), p.device)
                 buckets.setdefault(key, []).append((p, st, float(group["lr"]), float(group["eps"])))
         L = _lib.lib()
