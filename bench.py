@@ -449,6 +449,21 @@ def main():
         line["dedupe_identical_views"] = {"value": world * 1e3 / (ms_d / args.steps), "unit": UNIT, "ms_per_step": ms_d / args.steps,
                                           "note": "opt-in; 2 renders instead of 3 when train and event camera coincide; no gradient exchange in this extra"}
 
+    if use_fused and world == 1:
+        # extra: the whole training step of train.py:95-332 (iteration + densification statistics + both
+        # Adam steps) through event_3dgs_b200.trainer on a copy of the model, densification itself
+        # outside the window (it runs every 100th iteration; timed separately in profiles/r1_densify_bench.json)
+        from event_3dgs_b200 import trainer as tr
+        pc_t = pl.GaussianParams(scene["gaussians"], dev)
+        t_opt = tr.optimization_defaults(densify_from_iter=10 ** 9)
+        trn = tr.Trainer(pc_t, cams, cams, lambda i: gt_dev, opt=t_opt, event=True, deblur=deblur, extent=2.6)
+        for s in range(3):
+            trn.step()
+        ms_t, _, _ = timed(lambda s: trn.step(), args.steps)
+        line["train_loop"] = {"value": 1e3 / (ms_t / args.steps), "unit": UNIT, "ms_per_step": ms_t / args.steps,
+                              "what": "iteration + densification statistics + fused Adam (6 groups) + Adam(c), one view-pair per step"}
+        del trn, pc_t
+
     if rank == 0 and world == 1:
         # reference CUDA build (oracle/_ref) on the same tensors, same timing window
         if not args.no_ref_cuda:
@@ -494,8 +509,43 @@ def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves
         it(s)
     steps = max(3, min(args.steps, 10))
     ms, _, _ = timed(it, steps)
-    return {"value": 1e3 / (ms / steps), "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
-            "what": "reference diff-gaussian-rasterization sources compiled for sm_100a (oracle/_ref) + PyTorch SH/loss"}
+    out = {"value": 1e3 / (ms / steps), "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
+           "what": "reference diff-gaussian-rasterization sources compiled for sm_100a (oracle/_ref) + PyTorch SH/loss"}
+    # the reference's whole training step: the same iteration + its densification statistics
+    # (train.py:319-320) + torch.optim.Adam on its six groups + Adam(c)
+    from event_3dgs_b200 import trainer as tr
+    pc_r = pl.GaussianParams({k: v.detach().cpu().numpy() for k, v in
+                              dict(xyz=pc._xyz, features_dc=pc._features_dc, features_rest=pc._features_rest, scaling=pc._scaling,
+                                   rotation=pc._rotation, opacity=pc._opacity).items()}, pc._xyz.device)
+    pc_r.active_sh_degree = pc.active_sh_degree
+    groups = tr.training_setup(pc_r, tr.optimization_defaults(), 2.6).param_groups
+    opt_r = torch.optim.Adam([{"params": g["params"], "lr": g["lr"], "name": g["name"]} for g in groups], lr=0.0, eps=1e-15)
+    c_r = torch.nn.Parameter(torch.tensor(0.17, device=pc._xyz.device))
+    opt_c = torch.optim.Adam([c_r], lr=0.1)
+    P = pc_r._xyz.shape[0]
+    max_radii2D = torch.zeros(P, device=pc._xyz.device)
+    accum, denom = torch.zeros(P, 1, device=pc._xyz.device), torch.zeros(P, 1, device=pc._xyz.device)
+
+    def train_it(s):
+        v = view_of(args.warmup + s)
+        loss, pkg = pl.event_iteration(pc_r, cams[v], cams[v], cams[v + 1], gt, c_r, bg, deblur=deblur, render_fn=render_ref)
+        loss.backward()
+        with torch.no_grad():
+            vis, radii, vsp = pkg["visibility_filter"], pkg["radii"], pkg["viewspace_points"]
+            max_radii2D[vis] = torch.max(max_radii2D[vis], radii[vis])
+            accum[vis] += torch.norm(vsp.grad[vis, :2], dim=-1, keepdim=True)
+            denom[vis] += 1
+            opt_r.step()
+            opt_r.zero_grad(set_to_none=True)
+            opt_c.step()
+            opt_c.zero_grad(set_to_none=True)
+
+    for s in range(3):
+        train_it(s)
+    ms_t, _, _ = timed(train_it, steps)
+    out["train_loop"] = {"value": 1e3 / (ms_t / steps), "unit": UNIT, "ms_per_step": ms_t / steps,
+                         "what": "the same + densification statistics + torch.optim.Adam (train.py:317-332)"}
+    return out
 
 
 if __name__ == "__main__":
