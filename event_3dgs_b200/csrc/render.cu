@@ -48,6 +48,40 @@ __device__ __forceinline__ uint32_t subtile_mask(float x, float y, float hx, flo
 	return m;
 }
 
+// Shared-memory reads through an explicit 32-bit shared address, computed once per thread. With
+// plain array indexing the compiler re-derives the CTA's shared window base (S2UR SR_CgaCtaId +
+// UMOV + ULEA) at every use inside the inner loop; these keep it in one register.
+__device__ __forceinline__ uint32_t smem_addr(const void* p)
+{
+	uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+	asm volatile("" : "+r"(a));     // opaque: keep it in a register instead of re-materialising it
+	return a;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr)
+{
+	float4 v;
+	asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ float lds_f(uint32_t addr)
+{
+	float v;
+	asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr)
+{
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr)
+{
+	uint32_t v;
+	asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+	return v;
+}
+
 // forward.cu:335 with the reference's contraction
 __device__ __forceinline__ float eval_power(float dx, float dy, float cx, float cy, float cz)
 {
@@ -81,6 +115,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 	bool done = !inside;
 	float T = 1.0f;
 	uint32_t last_contributor = 0;
+	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask);
 	float Cacc[C];
 #pragma unroll
 	for (int c = 0; c < C; c++) Cacc[c] = 0.f;
@@ -103,13 +138,13 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 		const int nb = min(kBatch, total - b0);
 		for (int c0 = 0; c0 < nb; c0 += 32) {
 			const int jj = c0 + lane;
-			uint32_t m = __ballot_sync(E3_FULL, jj < nb && ((sMask[jj] >> w) & 1u));
+			uint32_t m = __ballot_sync(E3_FULL, jj < nb && ((lds_u8(aMask + jj) >> w) & 1u));
 			while (m) {
 				const int j = c0 + __ffs(m) - 1;
 				m &= m - 1;
 				if (done) continue;
-				const float4 a = sAB[2 * j];
-				const float4 b = sAB[2 * j + 1];
+				const float4 a = lds_f4(aAB + 32 * j);
+				const float4 b = lds_f4(aAB + 32 * j + 16);
 				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
 				const float power = eval_power(dx, dy, a.z, a.w, b.x);
 				if (power > 0.0f) continue;
@@ -120,7 +155,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 				Cacc[0] = __fmaf_rn(T, __fmul_rn(alpha, b.z), Cacc[0]);
 				if (C == 3) {
 					Cacc[1] = __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]);
-					Cacc[2] = __fmaf_rn(T, __fmul_rn(alpha, sC[j]), Cacc[2]);
+					Cacc[2] = __fmaf_rn(T, __fmul_rn(alpha, lds_f(aC + 4 * j)), Cacc[2]);
 				}
 				T = test_T;
 				last_contributor = (uint32_t)(b0 + j + 1);
@@ -217,6 +252,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	}
 	float last_alpha = 0.f;
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask), aId = smem_addr(sId);
 
 	// instance index within the tile's list, walked from total-1 down to 0; an instance with
 	// 0-based index i has contributor number i (reference: `contributor--` before the test,
@@ -241,16 +277,19 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 		const int j0 = max(0, (total - b0) - wmax);
 		for (int c0 = (j0 & ~31); c0 < nb; c0 += 32) {
 		const int jj = c0 + lane;
-		uint32_t m = __ballot_sync(E3_FULL, jj < nb && jj >= j0 && ((sMask[jj] >> w) & 1u));
+		uint32_t m = __ballot_sync(E3_FULL, jj < nb && jj >= j0 && ((lds_u8(aMask + jj) >> w) & 1u));
 		while (m) {
 			const int j = c0 + __ffs(m) - 1;
 			m &= m - 1;
 			const int contributor = total - 1 - (b0 + j);
-			const float4 a = sAB[2 * j];
-			const float4 b = sAB[2 * j + 1];
+			const float4 a = lds_f4(aAB + 32 * j);
+			const float4 b = lds_f4(aAB + 32 * j + 16);
 			const float dx = a.x - pixfx, dy = a.y - pixfy;
 			const float power = eval_power(dx, dy, a.z, a.w, b.x);
-			const float G = expf(power);
+			// ex2.approx of power * log2(e): within 5e-7 relative of the forward's accurate expf, far inside
+			// the gradient tolerance (1e-4), 6 instructions shorter per examined pair
+			float G;
+			asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * 1.4426950408889634f));
 			const float alpha = fminf(0.99f, b.y * G);
 			const bool valid = (contributor < last_contributor) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
 			if (!__any_sync(E3_FULL, valid)) continue;
@@ -260,12 +299,14 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 #pragma unroll
 			for (int i = 0; i < 8; i++) v[i] = 0.f;
 			if (valid) {
-				// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path)
-				const float ra = __frcp_rn(1.f - alpha);
+				// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path;
+				// rcp.approx is within 1 ulp and 1 - alpha lies in [0.01, 0.996], no special cases)
+				float ra;
+				asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(1.f - alpha));
 				T = T * ra;
 				const float dchannel_dcolor = alpha * T;
 				float col[3];
-				col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? sC[j] : 0.f;
+				col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? lds_f(aC + 4 * j) : 0.f;
 				float dL_dalpha = 0.0f;
 #pragma unroll
 				for (int c = 0; c < C; c++) {
@@ -294,12 +335,12 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 #pragma unroll
 				for (int o = 16; o; o >>= 1) v8 += __shfl_xor_sync(E3_FULL, v8, o);
 			}
-			float* dst = acc + (size_t)sId[j] * E3_ACC_STRIDE;
 			if ((lane & 3) == 0) {
+				float* dst = acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE;
 				const int slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
 				if (C == 3 || slot < 7) atomicAdd(dst + slot, v[0]);
 			}
-			if (C == 3 && lane == 1) atomicAdd(dst + 8, v8);
+			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + 8, v8);
 		}
 		}
 	}
