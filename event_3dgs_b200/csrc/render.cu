@@ -275,13 +275,13 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 		const int nb = min(kBatch, total - b0);
 		// skip the part of the batch that lies behind this warp's deepest contributor
 		const int j0 = max(0, (total - b0) - wmax);
+		const int jlim = total - 1 - b0 - last_contributor;
 		for (int c0 = (j0 & ~31); c0 < nb; c0 += 32) {
 		const int jj = c0 + lane;
 		uint32_t m = __ballot_sync(E3_FULL, jj < nb && jj >= j0 && ((lds_u8(aMask + jj) >> w) & 1u));
 		while (m) {
 			const int j = c0 + __ffs(m) - 1;
 			m &= m - 1;
-			const int contributor = total - 1 - (b0 + j);
 			const float4 a = lds_f4(aAB + 32 * j);
 			const float4 b = lds_f4(aAB + 32 * j + 16);
 			const float dx = a.x - pixfx, dy = a.y - pixfy;
@@ -290,46 +290,50 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			// the gradient tolerance (1e-4), 6 instructions shorter per examined pair
 			float G;
 			asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * 1.4426950408889634f));
-			const float alpha = fminf(0.99f, b.y * G);
-			const bool valid = (contributor < last_contributor) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
+			float alpha = fminf(0.99f, b.y * G);
+			// contributor = total - 1 - (b0 + j) < last_contributor  <=>  j > jlim
+			const bool valid = (j > jlim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
 			if (!__any_sync(E3_FULL, valid)) continue;
 
+			// Branch-free from here: a lane without a contribution runs the same arithmetic with
+			// alpha = G = 0, which leaves its state untouched (T * 1, selects) and makes all of its
+			// addends exact zeros.
+			alpha = valid ? alpha : 0.f;
+			G = valid ? G : 0.f;
 			float v[8];
 			float v8 = 0.f;
+			// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path;
+			// rcp.approx is within 1 ulp and 1 - alpha lies in [0.01, 1], no special cases)
+			float ra;
+			asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(1.f - alpha));
+			T = T * ra;
+			const float dchannel_dcolor = alpha * T;
+			float col[3];
+			col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? lds_f(aC + 4 * j) : 0.f;
+			float dL_dalpha = 0.0f;
 #pragma unroll
-			for (int i = 0; i < 8; i++) v[i] = 0.f;
-			if (valid) {
-				// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path;
-				// rcp.approx is within 1 ulp and 1 - alpha lies in [0.01, 0.996], no special cases)
-				float ra;
-				asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(1.f - alpha));
-				T = T * ra;
-				const float dchannel_dcolor = alpha * T;
-				float col[3];
-				col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? lds_f(aC + 4 * j) : 0.f;
-				float dL_dalpha = 0.0f;
-#pragma unroll
-				for (int c = 0; c < C; c++) {
-					accum_rec[c] = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
-					last_color[c] = col[c];
-					dL_dalpha += (col[c] - accum_rec[c]) * dL_dpixel[c];
-				}
-				dL_dalpha *= T;
-				last_alpha = alpha;
-				dL_dalpha += (-T_final * ra) * bg_dot_dpixel;
-				const float dL_dG = b.y * dL_dalpha;
-				const float gdx = G * dx, gdy = G * dy;
-				const float dG_ddelx = -gdx * a.z - gdy * a.w;
-				const float dG_ddely = -gdy * b.x - gdx * a.w;
-				v[0] = dL_dG * dG_ddelx * ddelx_dx;
-				v[1] = dL_dG * dG_ddely * ddely_dy;
-				v[2] = -0.5f * gdx * dx * dL_dG;
-				v[3] = -0.5f * gdx * dy * dL_dG;
-				v[4] = -0.5f * gdy * dy * dL_dG;
-				v[5] = G * dL_dalpha;
-				v[6] = dchannel_dcolor * dL_dpixel[0];
-				if (C == 3) { v[7] = dchannel_dcolor * dL_dpixel[1]; v8 = dchannel_dcolor * dL_dpixel[2]; }
+			for (int c = 0; c < C; c++) {
+				const float ar = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
+				accum_rec[c] = valid ? ar : accum_rec[c];
+				last_color[c] = valid ? col[c] : last_color[c];
+				dL_dalpha += (col[c] - ar) * dL_dpixel[c];
 			}
+			dL_dalpha *= T;
+			last_alpha = valid ? alpha : last_alpha;
+			dL_dalpha += (-T_final * ra) * bg_dot_dpixel;
+			const float dL_dG = b.y * dL_dalpha;
+			const float gdx = G * dx, gdy = G * dy;
+			const float dG_ddelx = -gdx * a.z - gdy * a.w;
+			const float dG_ddely = -gdy * b.x - gdx * a.w;
+			v[0] = dL_dG * dG_ddelx * ddelx_dx;
+			v[1] = dL_dG * dG_ddely * ddely_dy;
+			v[2] = -0.5f * gdx * dx * dL_dG;
+			v[3] = -0.5f * gdx * dy * dL_dG;
+			v[4] = -0.5f * gdy * dy * dL_dG;
+			v[5] = G * dL_dalpha;
+			v[6] = dchannel_dcolor * dL_dpixel[0];
+			v[7] = 0.f;
+			if (C == 3) { v[7] = dchannel_dcolor * dL_dpixel[1]; v8 = dchannel_dcolor * dL_dpixel[2]; }
 			warp_reduce8(v, lane);
 			if (C == 3) {
 #pragma unroll
