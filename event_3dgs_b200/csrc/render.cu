@@ -142,23 +142,24 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 			while (m) {
 				const int j = c0 + __ffs(m) - 1;
 				m &= m - 1;
-				if (done) continue;
 				const float4 a = lds_f4(aAB + 32 * j);
 				const float4 b = lds_f4(aAB + 32 * j + 16);
 				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
 				const float power = eval_power(dx, dy, a.z, a.w, b.x);
-				if (power > 0.0f) continue;
+				// branch-free: every lane evaluates, selects keep the state of lanes that skip
 				const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
-				if (alpha < 1.0f / 255.0f) continue;
+				const bool contrib = !done && power <= 0.0f && alpha >= 1.0f / 255.0f;
 				const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
-				if (test_T < 0.0001f) { done = true; continue; }
-				Cacc[0] = __fmaf_rn(T, __fmul_rn(alpha, b.z), Cacc[0]);
+				const bool blend = contrib && test_T >= 0.0001f;
+				done = done || (contrib && !blend);
+				const float wgt = __fmul_rn(alpha, b.z);
+				Cacc[0] = blend ? __fmaf_rn(T, wgt, Cacc[0]) : Cacc[0];
 				if (C == 3) {
-					Cacc[1] = __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]);
-					Cacc[2] = __fmaf_rn(T, __fmul_rn(alpha, lds_f(aC + 4 * j)), Cacc[2]);
+					Cacc[1] = blend ? __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]) : Cacc[1];
+					Cacc[2] = blend ? __fmaf_rn(T, __fmul_rn(alpha, lds_f(aC + 4 * j)), Cacc[2]) : Cacc[2];
 				}
-				T = test_T;
-				last_contributor = (uint32_t)(b0 + j + 1);
+				T = blend ? test_T : T;
+				last_contributor = blend ? (uint32_t)(b0 + j + 1) : last_contributor;
 			}
 			if (__all_sync(E3_FULL, done)) break;
 		}
