@@ -298,6 +298,28 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 		}
 		rec[3 * idx + 1] = make_float4(conic.z, opac, col[0], col[1]);
 		rec[3 * idx + 2] = make_float4(col[2], ext_x, ext_y, 0.f);
+		if (RAW) {
+			// Fused path only (its instance lists are not observable): the reference's rect comes
+			// from the 3-sigma radius, but a pixel is touched only inside the { alpha >= 1/255 } box
+			// above, which for low opacities is much smaller. Tiles outside it would be sorted,
+			// loaded and then skipped by every pixel, so they are not emitted at all (about 28 % of
+			// the instances of the BASELINE c3 scene). Results do not change by a bit; radii (the
+			// visibility filter) stay the reference's.
+			if (!(ext_x >= 0.f)) {
+				tt = 0;
+			} else {
+				const int tx0 = max((int)x0, (int)floorf((pix - ext_x) * (1.0f / E3_TILE_X)));
+				const int tx1 = min((int)x1, (int)floorf((pix + ext_x) * (1.0f / E3_TILE_X)) + 1);
+				const int ty0 = max((int)y0, (int)floorf((piy - ext_y) * (1.0f / E3_TILE_Y)));
+				const int ty1 = min((int)y1, (int)floorf((piy + ext_y) * (1.0f / E3_TILE_Y)) + 1);
+				if (tx1 <= tx0 || ty1 <= ty0) {
+					tt = 0;
+				} else {
+					tt = (uint32_t)((ty1 - ty0) * (tx1 - tx0));
+					rc = make_uint2((uint32_t)tx0 | ((uint32_t)tx1 << 16), (uint32_t)ty0 | ((uint32_t)ty1 << 16));
+				}
+			}
+		}
 	} while (0);
 	radii[idx] = my_radius;
 	tiles_touched[idx] = tt;
