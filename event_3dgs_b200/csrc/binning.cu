@@ -145,6 +145,18 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev)
 {
 	if (n_dev) n = min(n, (size_t)*n_dev);
+	// All keys agree on this digit (the global histogram has a single non-empty bin): the stable pass
+	// is the identity permutation, so the tile is copied to the other buffer without ranking or
+	// look-back. Typical for the top byte of the depth keys (sign + 7 exponent bits: all depths of a
+	// scene inside [2^k, 4 * 2^k)).
+	if (__syncthreads_or(threadIdx.x <= mask && ghist[threadIdx.x] == (uint32_t)n && n > 0)) {
+		const size_t t0 = (size_t)blockIdx.x * E3_SORT_TILE;
+		for (size_t k = t0 + threadIdx.x; k < min(n, t0 + (size_t)E3_SORT_TILE); k += E3_SORT_THREADS) {
+			keys_out[k] = keys_in[k];
+			vals_out[k] = vals_in[k];
+		}
+		return;
+	}
 	__shared__ uint32_t wcnt[8][256];
 	__shared__ uint32_t s_keys[E3_SORT_TILE];
 	__shared__ uint32_t s_vals[E3_SORT_TILE];

@@ -244,8 +244,13 @@ def test_accumulate_over_view_pairs(cuda_dev):
     g2 = [p.grad.clone() for p in leaves]
     fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
     fused.event_iteration_backward(pc, cams[4], cams[4], cams[5], gt, c, bg, accumulate=True)
-    for p, a, b in zip(leaves, g1, g2):
-        assert rel_err(p.grad.cpu().numpy(), (a + b).cpu().numpy(), 1e-20) < 1e-4
+    # Three separate runs are compared, and float atomics commit in a different order every run: the
+    # gradients that pass through the ill-conditioned conic -> covariance chain (xyz, scaling, rotation)
+    # repeat only to ~3e-4 of their scale from run to run -- the reference CUDA build shows the same
+    # spread (profiles/r1_grad_run_to_run_spread.json, tools/grad_spread.py). The others repeat to 1e-6.
+    tol = [2e-3, 1e-4, 1e-4, 2e-3, 2e-3, 1e-4, 1e-4]
+    for p, a, b, t in zip(leaves, g1, g2, tol):
+        assert rel_err(p.grad.cpu().numpy(), (a + b).cpu().numpy(), 1e-20) < t
 
 
 def test_no_sync_workspace_path_and_overflow_recovery(cuda_dev):
