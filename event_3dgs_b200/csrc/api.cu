@@ -453,25 +453,35 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, 1.0f, a->views[1].channels, a->loss_scratch, 64,
 		a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, main_st);
 	if (rc) return rc;
-	// ---- three backward blends concurrently, then the three gradient accumulations in order ----
+	// ---- per view, on its own stream: backward blend, then the gradient accumulation. The three
+	// views add into the same (zeroed) gradient tensors with vector reductions, so nothing serialises
+	// behind the blends and the latency-bound accumulation kernels fill the gaps the blends leave. ----
+	if (!a->accumulate) {
+		const size_t P = (size_t)a->P;
+		E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_features_dc, 0, P * 3 * sizeof(float), main_st));
+		if (a->d_features_rest && a->active_sh_degree > 0) E3_CHECK(cudaMemsetAsync(a->d_features_rest, 0, P * 45 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_opacity_logits, 0, P * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_log_scales, 0, P * 3 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_raw_rotations, 0, P * 4 * sizeof(float), main_st));
+	}
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
-	for (int phase = 1; phase <= 2; phase++) {
-		for (int k = 0; k < 3; k++) {
-			const e3_view& v = a->views[k];
-			rc = backward_raw_impl(phase, a->P, a->active_sh_degree, v.channels, (int)a->binning_capacity, a->background, a->width,
+	for (int k = 0; k < 3; k++) {
+		const e3_view& v = a->views[k];
+		{
+			rc = backward_raw_impl(3, a->P, a->active_sh_degree, v.channels, (int)a->binning_capacity, a->background, a->width,
 				a->height, a->xyz, a->features_dc, a->features_rest, a->opacity_logits, a->log_scales, a->scale_modifier,
 				a->raw_rotations, v.viewmatrix, v.projmatrix, v.cam_pos, v.tan_fovx, v.tan_fovy, v.radii, v.geometry_buffer,
-				v.binning_buffer, v.image_buffer, v.seed, (k > 0 || a->accumulate) ? 1 : 0, a->d_xyz, a->d_features_dc,
+				v.binning_buffer, v.image_buffer, v.seed, 1, a->d_xyz, a->d_features_dc,
 				a->d_features_rest, a->d_opacity_logits, a->d_log_scales, a->d_raw_rotations, k == 0 ? a->d_mean2D : nullptr, 0,
-				phase == 1 ? sts[k] : main_st);
+				sts[k]);
 			if (rc) return rc;
 		}
-		if (phase == 1)
-			for (int k = 1; k < 3; k++) {
-				E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
-				E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
-			}
+	}
+	for (int k = 1; k < 3; k++) {
+		E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
+		E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
 	}
 	return 0;
 }

@@ -412,9 +412,17 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 }
 
 template <bool ACC>
-__device__ __forceinline__ void put(float* p, float v) { if (ACC) *p += v; else *p = v; }
+__device__ __forceinline__ void put(float* p, float v) { if (ACC) atomicAdd(p, v); else *p = v; }
 
-// coalesced write-out of a staged [rows,K] tile (float4 where the global row start is aligned)
+// 16-byte vector reduction into global memory (REDG.E.ADD.F32x4): accumulation without a read
+// round trip, and safe against the other views' kernels accumulating into the same rows concurrently
+__device__ __forceinline__ void red_add4(float4* p, const float4 v)
+{
+	asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// coalesced write-out of a staged [rows,K] tile (float4 where the global row start is aligned).
+// ACC: atomic accumulation (all-zero vectors, e.g. the rows of culled Gaussians, are skipped).
 template <bool ACC>
 __device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float* sm, int nfl)
 {
@@ -423,13 +431,13 @@ __device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float*
 		float4* d4 = reinterpret_cast<float4*>(dst);
 		const float4* s4 = reinterpret_cast<const float4*>(sm);
 		for (int i = threadIdx.x; i < nv; i += blockDim.x) {
-			float4 v = s4[i];
-			if (ACC) { const float4 o = d4[i]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-			d4[i] = v;
+			const float4 v = s4[i];
+			if (ACC) { if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add4(d4 + i, v); }
+			else d4[i] = v;
 		}
-		for (int i = (nv << 2) + threadIdx.x; i < nfl; i += blockDim.x) dst[i] = ACC ? dst[i] + sm[i] : sm[i];
+		for (int i = (nv << 2) + threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) atomicAdd(dst + i, sm[i]); } else dst[i] = sm[i]; }
 	} else {
-		for (int i = threadIdx.x; i < nfl; i += blockDim.x) dst[i] = ACC ? dst[i] + sm[i] : sm[i];
+		for (int i = threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) atomicAdd(dst + i, sm[i]); } else dst[i] = sm[i]; }
 	}
 }
 
@@ -437,8 +445,8 @@ __device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float*
 
 // RAW: gradients are taken all the way to the leaf parameters (chain rule through exp /
 // normalize / sigmoid and the SH evaluation, i.e. the autograd backward of K15 in SURVEY.md 2b).
-// ACC: add to the output rows instead of overwriting them (renders 2 and 3 of an event iteration
-// accumulate into the gradient tensors written by render 1). SHREST: features_rest and its
+// ACC: add to the output rows (atomically) instead of overwriting them: the three renders of an event
+// iteration accumulate into the same gradient tensors, from three streams. SHREST: features_rest and its
 // gradient are staged through shared memory as [128,45] tiles (RAW with degree > 0).
 // Pointer roles in RAW mode: shs = features_dc [P,3], f_rest = features_rest [P,15,3],
 // dL_dsh = d features_dc, d_frest = d features_rest, dL_dopacity = d opacity logit,
@@ -686,15 +694,14 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 		s_scl[3 * t] = ds[0]; s_scl[3 * t + 1] = ds[1]; s_scl[3 * t + 2] = ds[2];
 		if (live && (!ACC || vis)) {
 			float4* dr = reinterpret_cast<float4*>(dL_drot) + idx;
-			if (ACC) { const float4 o = *dr; dq.x += o.x; dq.y += o.y; dq.z += o.z; dq.w += o.w; }
-			*dr = dq;
+			if (ACC) red_add4(dr, dq); else *dr = dq;
 		}
 	}
 	__syncthreads();
 	flush_rows<ACC>(dL_dmean3D + first * 3, s_mean, rows * 3);
 	if (scales) flush_rows<ACC>(dL_dscale + first * 3, s_scl, rows * 3);
 	if (RAW) flush_rows<ACC>(dL_dsh + first * 3, s_fdc, rows * 3);
-	if (dL_dmean2D) flush_rows<ACC>(dL_dmean2D + first * 3, s_cov, rows * 3);
+	if (dL_dmean2D) flush_rows<false>(dL_dmean2D + first * 3, s_cov, rows * 3);   // this view's own screen-space gradient: assigned
 	if (SHREST) flush_rows<ACC>(d_frest + first * 45, s_dsh, rows * 45);
 }
 

@@ -307,11 +307,12 @@ E3_API int e3_l1_ssim_loss(int width, int height, int gray, const float* image, 
  * any host synchronisation (e3_rasterize_forward_raw_ws x3, e3_event_loss, e3_rasterize_backward_raw
  * x3). Exists because at event-camera resolutions the ~75 kernels of an iteration are shorter than
  * the host work of seven separate binding calls. Everything is caller-owned and may be reused
- * from call to call, which also makes the call sequence fixed (capturable by the caller).
+ * from call to call.
  * views[0] = intensity view (3 channels), views[1], views[2] = event views `index`, `index+1`
  * (channels 1 = luma, or 3). seed buffers are [channels,H,W]. d_* receive the SUM of the three
- * backward passes (overwritten, or added to when accumulate != 0); d_mean2D (optional) is the
- * screen-space gradient of views[0]. out5 as in e3_event_loss. After the stream has passed the
+ * backward passes (zeroed first, or added to when accumulate != 0; the three views run on three
+ * streams and add with vector reductions, so the summation order, like that of the blend's atomics,
+ * is not fixed from run to run); d_mean2D (optional) is the screen-space gradient of views[0]. out5 as in e3_event_loss. After the stream has passed the
  * read-backs, check views[k].num_rendered_host[0] <= binning_capacity (see
  * e3_rasterize_forward_raw_ws). */
 typedef struct e3_view {
