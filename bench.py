@@ -452,6 +452,18 @@ def main():
                             "algorithmic_bytes_per_launch": algo,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                             "note": "the blend kernels are issue/latency bound, not HBM bound; see DESIGN.md"}
+        # the blend kernels are issue bound: the second roofline is the warp-instruction rate, with the
+        # instruction count per launch taken from the same committed ncu capture
+        try:
+            wi = ((tj["render_bwd_kernel<3>"]["warp_inst_per_launch"] + 2 * tj["render_bwd_kernel<1>"]["warp_inst_per_launch"]) / 3
+                  if cfg_name == "c3" else None)
+        except Exception:
+            wi = None
+        if wi and clk and clk.get("sm_mhz"):
+            peak_issue = 148 * 4 * clk["sm_mhz"] * 1e6
+            line["roofline_issue"] = {"bound": "issue", "kernel": "render_bwd_kernel", "achieved": wi / (per_launch_ms * 1e-3),
+                                      "peak": peak_issue, "unit": "warp instructions/s", "frac": wi / (per_launch_ms * 1e-3) / peak_issue,
+                                      "note": "warp instructions per launch from profiles/r1_traffic.json (ncu), mean over the one C=3 and two C=1 launches of a step; launch time live (three concurrent streams share the SMs, so this is a lower bound of the kernel's own rate), peak = 148 SMs x 4 schedulers x SM clock under load"}
     b_iter = sum(bytes_render(P, r, N, T) for r in Rs) + 108 * N + (24 * N if deblur else 0)
     line["iter_roofline"] = {"algorithmic_bytes": b_iter, "achieved_gbs": b_iter / (ms_per_step * 1e-3) / 1e9,
                              "frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak}

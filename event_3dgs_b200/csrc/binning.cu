@@ -111,6 +111,9 @@ __global__ void __launch_bounds__(E3_SCAN_THREADS) scan_down_kernel(const uint32
 // (single-word flag|count descriptors), reorders the tile in shared memory and writes each digit
 // run to global memory with consecutive threads on consecutive addresses. Stable.
 // Scratch (uint32 words): ghist[4][256] | tile_counter[8] | lookback[npass][ntiles][256].
+#ifndef E3_SORT_LOOKBACK
+#define E3_SORT_LOOKBACK 16
+#endif
 #define E3_LB_AGG 0x40000000u
 #define E3_LB_PREFIX 0x80000000u
 #define E3_LB_MASK 0x3fffffffu
@@ -211,17 +214,18 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	const uint32_t gb = block_excl_scan(mine ? ghist[threadIdx.x] : 0u, s_warp, tot_all);
 	const uint32_t ls = block_excl_scan(total, s_warp, tot_all);
 	if (mine) {
-		// look back over earlier tiles, 8 descriptors per step: the loads of a step are independent,
+		// look back over earlier tiles, E3_SORT_LOOKBACK descriptors per step: the loads of a step are independent,
 		// so a long run of tiles that have only published their aggregate costs one memory round trip
 		// per 8 tiles instead of one per tile
 		uint32_t excl = 0;
 		bool found = (tile == 0);
-		for (int t = (int)tile - 1; t >= 0 && !found; t -= 8) {
-			uint32_t v[8];
+		constexpr int LB = E3_SORT_LOOKBACK;
+		for (int t = (int)tile - 1; t >= 0 && !found; t -= LB) {
+			uint32_t v[LB];
 #pragma unroll
-			for (int k = 0; k < 8; k++) v[k] = (t - k >= 0) ? lookback[(size_t)(t - k) * 256 + threadIdx.x] : E3_LB_PREFIX;
+			for (int k = 0; k < LB; k++) v[k] = (t - k >= 0) ? lookback[(size_t)(t - k) * 256 + threadIdx.x] : E3_LB_PREFIX;
 #pragma unroll
-			for (int k = 0; k < 8; k++) {
+			for (int k = 0; k < LB; k++) {
 				if (found) break;
 				while ((v[k] & (E3_LB_AGG | E3_LB_PREFIX)) == 0) { __nanosleep(20); v[k] = lookback[(size_t)(t - k) * 256 + threadIdx.x]; }
 				excl += v[k] & E3_LB_MASK;
