@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(E3_SCAN_THREADS) scan_down_kernel(const uint32
 // locally, obtains the number of equal digits in all earlier tiles by decoupled look-back
 // (single-word flag|count descriptors), reorders the tile in shared memory and writes each digit
 // run to global memory with consecutive threads on consecutive addresses. Stable.
-// Scratch (uint32 words): ghist[4][256] | tile_counter[8] | lookback[npass][ntiles][256].
+// Scratch (uint32 words): ghist[4][256] | tile_counter[8] | per pass: tile_desc[ntiles][256], group_desc[ngroups][256].
 #ifndef E3_SORT_LOOKBACK
 #define E3_SORT_LOOKBACK 16
 #endif
@@ -147,6 +147,7 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist, volatile uint32_t* lookback,
 	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev)
 {
+	const uint32_t ntiles = gridDim.x;     // the launch is sized for the capacity, the descriptor arrays with it
 	if (n_dev) n = min(n, (size_t)*n_dev);
 	// All keys agree on this digit (the global histogram has a single non-empty bin): the stable pass
 	// is the identity permutation, so the tile is copied to the other buffer without ranking or
@@ -203,36 +204,54 @@ __global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const u
 	// per digit (thread d): tile total, look-back over earlier tiles, warp offsets
 	uint32_t total = 0;
 	const bool mine = threadIdx.x <= mask;
+	volatile uint32_t* tile_desc = lookback;                                   // [ntiles][256], aggregate only
+	volatile uint32_t* group_desc = lookback + (size_t)ntiles * 256;           // [ngroups][256], aggregate or inclusive prefix
+	const uint32_t grp = tile / E3_SORT_GROUP, rin = tile % E3_SORT_GROUP;
 	if (mine) {
 #pragma unroll
 		for (int ww = 0; ww < 8; ww++) { const uint32_t c = wcnt[ww][threadIdx.x]; wcnt[ww][threadIdx.x] = total; total += c; }
-		volatile uint32_t* my = lookback + (size_t)tile * 256 + threadIdx.x;
-		*my = total | (tile == 0 ? E3_LB_PREFIX : E3_LB_AGG);
+		tile_desc[(size_t)tile * 256 + threadIdx.x] = total | E3_LB_AGG;
 	}
 	// exclusive scans over the digits: global bases from the histogram, local run starts from the totals
 	uint32_t tot_all;
 	const uint32_t gb = block_excl_scan(mine ? ghist[threadIdx.x] : 0u, s_warp, tot_all);
 	const uint32_t ls = block_excl_scan(total, s_warp, tot_all);
 	if (mine) {
-		// look back over earlier tiles, E3_SORT_LOOKBACK descriptors per step: the loads of a step are independent,
-		// so a long run of tiles that have only published their aggregate costs one memory round trip
-		// per 8 tiles instead of one per tile
-		uint32_t excl = 0;
-		bool found = (tile == 0);
+		// Two-level look-back. All tiles of a launch are co-resident (<= 2 per SM), so a flat look-back
+		// would walk over almost every earlier tile (O(tiles^2) descriptor reads). Instead: sum the
+		// aggregates of the earlier tiles of the own group (published before any look-back starts, so
+		// there is nothing to wait for), then walk the GROUP descriptors, which the last tile of each
+		// group publishes first as aggregate and then as inclusive prefix.
+		uint32_t in_group = 0;
 		constexpr int LB = E3_SORT_LOOKBACK;
-		for (int t = (int)tile - 1; t >= 0 && !found; t -= LB) {
+		for (int k0 = 0; k0 < (int)rin; k0 += LB) {
 			uint32_t v[LB];
 #pragma unroll
-			for (int k = 0; k < LB; k++) v[k] = (t - k >= 0) ? lookback[(size_t)(t - k) * 256 + threadIdx.x] : E3_LB_PREFIX;
+			for (int k = 0; k < LB; k++) v[k] = (k0 + k < (int)rin) ? tile_desc[(size_t)(tile - 1 - k0 - k) * 256 + threadIdx.x] : E3_LB_AGG;
+#pragma unroll
+			for (int k = 0; k < LB; k++) {
+				while ((v[k] & E3_LB_AGG) == 0) { __nanosleep(20); v[k] = tile_desc[(size_t)(tile - 1 - k0 - k) * 256 + threadIdx.x]; }
+				in_group += v[k] & E3_LB_MASK;
+			}
+		}
+		const bool closes_group = rin == E3_SORT_GROUP - 1;
+		if (closes_group && grp != 0) group_desc[(size_t)grp * 256 + threadIdx.x] = (in_group + total) | E3_LB_AGG;
+		uint32_t before = 0;
+		bool found = (grp == 0);
+		for (int g = (int)grp - 1; g >= 0 && !found; g -= LB) {
+			uint32_t v[LB];
+#pragma unroll
+			for (int k = 0; k < LB; k++) v[k] = (g - k >= 0) ? group_desc[(size_t)(g - k) * 256 + threadIdx.x] : E3_LB_PREFIX;
 #pragma unroll
 			for (int k = 0; k < LB; k++) {
 				if (found) break;
-				while ((v[k] & (E3_LB_AGG | E3_LB_PREFIX)) == 0) { __nanosleep(20); v[k] = lookback[(size_t)(t - k) * 256 + threadIdx.x]; }
-				excl += v[k] & E3_LB_MASK;
+				while ((v[k] & (E3_LB_AGG | E3_LB_PREFIX)) == 0) { __nanosleep(20); v[k] = group_desc[(size_t)(g - k) * 256 + threadIdx.x]; }
+				before += v[k] & E3_LB_MASK;
 				if (v[k] & E3_LB_PREFIX) found = true;
 			}
 		}
-		if (tile != 0) { __threadfence(); lookback[(size_t)tile * 256 + threadIdx.x] = (excl + total) | E3_LB_PREFIX; }
+		const uint32_t excl = before + in_group;
+		if (closes_group) { __threadfence(); group_desc[(size_t)grp * 256 + threadIdx.x] = (excl + total) | E3_LB_PREFIX; }
 		s_gpos[threadIdx.x] = gb + excl;
 		s_lstart[threadIdx.x] = ls;
 	}
@@ -361,7 +380,7 @@ cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, 
 		radix_hist_all_kernel<<<hgrid, 256, 0, st>>>(keys[cur], n, plan, ghist, n_dev);
 		for (int p = 0; p < plan.npass; p++) {
 			radix_onesweep_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * nblk * 256, tile_counter + p, n_dev);
+				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * e3_sort_desc_words(n), tile_counter + p, n_dev);
 			cur ^= 1;
 		}
 		g_e3_launches += 1 + plan.npass;

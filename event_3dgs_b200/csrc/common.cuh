@@ -34,8 +34,12 @@ static inline void e3_carve(char*& p, T*& out, size_t count)
 #define E3_SCAN_TILE (E3_SCAN_THREADS * E3_SCAN_ITEMS)
 
 static inline size_t e3_sort_blocks(size_t n) { return (n + E3_SORT_TILE - 1) / E3_SORT_TILE; }
+// Look-back descriptors are two-level: one per tile and one per group of E3_SORT_GROUP tiles.
+#define E3_SORT_GROUP 32
+static inline size_t e3_sort_groups(size_t n) { return (e3_sort_blocks(n) + E3_SORT_GROUP - 1) / E3_SORT_GROUP; }
+static inline size_t e3_sort_desc_words(size_t n) { return (e3_sort_blocks(n) + e3_sort_groups(n)) * 256; }
 // uint32 words of radix-sort scratch: 4 global histograms, tile counters, look-back descriptors of 4 passes
-static inline size_t e3_sort_scratch_words(size_t n) { return 4 * 256 + 8 + 4 * e3_sort_blocks(n) * 256; }
+static inline size_t e3_sort_scratch_words(size_t n) { return 4 * 256 + 8 + 4 * e3_sort_desc_words(n); }
 static inline size_t e3_scan_blocks(size_t n) { return (n + E3_SCAN_TILE - 1) / E3_SCAN_TILE; }
 
 struct E3GeomState {
