@@ -8,7 +8,7 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # repo root
 from event_3dgs_b200 import densify as dn  # noqa: E402
 from oracle import densify_oracle as do  # noqa: E402
 from tests.test_densify_gpu import make_model, random_case  # noqa: E402

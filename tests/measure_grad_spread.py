@@ -11,7 +11,7 @@ import sys
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # repo root
 from tests import gpu_common as gc  # noqa: E402
 from tests.common import rel_err, scene_inputs, smooth_dL  # noqa: E402
 

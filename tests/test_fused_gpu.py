@@ -247,7 +247,7 @@ def test_accumulate_over_view_pairs(cuda_dev):
     # Three separate runs are compared, and float atomics commit in a different order every run: the
     # gradients that pass through the ill-conditioned conic -> covariance chain (xyz, scaling, rotation)
     # repeat only to ~3e-4 of their scale from run to run -- the reference CUDA build shows the same
-    # spread (profiles/r1_grad_run_to_run_spread.json, tools/grad_spread.py). The others repeat to 1e-6.
+    # spread (profiles/r1_grad_run_to_run_spread.json, tests/measure_grad_spread.py). The others repeat to 1e-6.
     tol = [2e-3, 1e-4, 1e-4, 2e-3, 2e-3, 1e-4, 1e-4]
     for p, a, b, t in zip(leaves, g1, g2, tol):
         assert rel_err(p.grad.cpu().numpy(), (a + b).cpu().numpy(), 1e-20) < t
