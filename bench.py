@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--P", type=int, default=None, help="override the number of Gaussians (debugging)")
     ap.add_argument("--pairs", type=int, default=None,
                     help="event view-pairs per optimizer step over all ranks (default: one per rank; c5: 64)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "nccl"],
+                    help="multi-GPU gradient exchange: auto = own NVLS all-reduce kernel when the box supports multicast, else NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=25.0)
@@ -280,10 +282,19 @@ def main():
         b = rank if b is None else b
         return 2 + (7 * (step * pairs + b)) % 80
 
+    exchange_used = {"kind": "none" if world == 1 else "nccl all-reduce (AVG) of the flat gradient buffer"}
+
     def iteration(step, gt, sync_grads=True, gt_ready=None):
         for p in leaves:
             p.grad = None
         loss = None
+        ex = None
+        if world > 1 and use_fused and args.exchange != "nccl" and fused._workspace_for(pc, cams[view_of(step, my_pairs[0])]) is not None:
+            # our own in-switch all-reduce kernel over the NVLS multicast alias of the gradient buffer
+            # (parallel.FusedGradientExchange, e3_nvls_allreduce); NCCL when the box has no multicast
+            ex = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), dev)
+        if use_fused:
+            pc._grad_exchange = ex
         for k, b in enumerate(my_pairs):
             v = view_of(step, b)
             if use_fused:
@@ -293,6 +304,11 @@ def main():
                 l, pkg = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur)
                 l.backward()              # autograd accumulates into .grad over the pairs
             loss = l if loss is None else loss + l
+        if ex is not None:
+            if sync_grads:
+                ex.allreduce(1.0 / pairs)
+                exchange_used["kind"] = "e3_nvls_allreduce (multimem.ld_reduce / multimem.st over the NVLS multicast alias), mean over all pairs"
+            return loss
         if len(my_pairs) > 1:             # mean over this rank's pairs (the all-reduce averages over ranks)
             if use_fused:
                 pc._grad_flat.div_(len(my_pairs))
@@ -420,6 +436,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if pairs == world else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload(cfg, cfg_name, args.kind, pairs)}
     line["config"]["path"] = path_name
+    line["config"]["gradient_exchange"] = exchange_used["kind"]
     line["config"]["num_rendered"] = Rs
     line["mpix_per_sec"] = value * 3 * N / 1e6
     line["config"]["unit_note"] = "one iteration = one event view-pair (3 renders fwd + event loss + bwd); value counts view-pairs per second over all ranks"

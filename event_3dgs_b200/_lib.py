@@ -88,11 +88,14 @@ class EventIterationArgs(ctypes.Structure):
                 ("views", View * 3),
                 ("gt_now", ctypes.c_void_p), ("gt_next", ctypes.c_void_p), ("gt_intensity", ctypes.c_void_p), ("gt_blur", ctypes.c_void_p),
                 ("gt_is_u8", ctypes.c_int), ("c", ctypes.c_void_p), ("out5", ctypes.c_void_p), ("loss_scratch", ctypes.c_void_p),
-                ("wait_before_loss_event", ctypes.c_void_p), ("forwards_done_event", ctypes.c_void_p)]
+                ("wait_before_loss_event", ctypes.c_void_p), ("forwards_done_event", ctypes.c_void_p),
+                ("loss_upstream", ctypes.c_float), ("grad_multicast_delta", ctypes.c_longlong)]
 
 
 SIGNATURES["e3_event_iteration"] = (_i, [ctypes.POINTER(EventIterationArgs), _vp])
 SIGNATURES["e3_adam_step"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, _vp])
+SIGNATURES["e3_multimem_add"] = (_i, [_vp, _vp, _sz, _f, _vp])
+SIGNATURES["e3_nvls_allreduce"] = (_i, [_vp, _sz, _i, _i, _f, _vp])
 SIGNATURES["e3_densification_stats"] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp])
 SIGNATURES["e3_densify_scratch_bytes"] = (_sz, [_i])
 SIGNATURES["e3_densify_plan"] = (_i, [_i, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _i, _vp, _sz, _vp, _vp])

@@ -309,17 +309,19 @@ static int backward_raw_impl(int phase,
 	const float* dL_dpix, int accumulate,
 	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
 	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
-	int debug, void* stream)
+	int debug, void* stream, long long mc_delta = 0)
 {
 	cudaStream_t st = (cudaStream_t)stream;
 	if (P < 0 || active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
 	if (P == 0) return 0;
+	if (mc_delta != 0 && !accumulate) return E3_ERR_BAD_ARGUMENT;      // multicast reductions only accumulate
 	if (!geometry_buffer || !image_buffer || (R > 0 && !binning_buffer) || !radii || !xyz || !features_dc || !opacity_logits ||
 		!log_scales || !raw_rotations || !dL_dpix || !d_xyz || !d_features_dc || !d_opacity_logits || !d_log_scales ||
 		!d_raw_rotations || !viewmatrix || !projmatrix || !campos)
 		return E3_ERR_BAD_ARGUMENT;
 	if (active_sh_degree > 0 && (!features_rest || !d_features_rest)) return E3_ERR_BAD_ARGUMENT;
 	E3Frame f = make_frame(P, active_sh_degree, 16, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
+	f.mc_delta = mc_delta;
 	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
 	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
@@ -450,12 +452,14 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	if (a->P == 0) return 0;
 	if (a->wait_before_loss_event) E3_CHECK(cudaStreamWaitEvent(main_st, (cudaEvent_t)a->wait_before_loss_event, 0));
 	int rc = e3_event_loss(a->width, a->height, a->views[0].out_color, a->views[1].out_color, a->views[2].out_color, a->gt_now,
-		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, 1.0f, a->views[1].channels, a->loss_scratch, 64,
+		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, a->loss_upstream != 0.f ? a->loss_upstream : 1.0f,
+		a->views[1].channels, a->loss_scratch, 64,
 		a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, main_st);
 	if (rc) return rc;
 	// ---- per view, on its own stream: backward blend, then the gradient accumulation. The three
 	// views add into the same (zeroed) gradient tensors with vector reductions, so nothing serialises
 	// behind the blends and the latency-bound accumulation kernels fill the gaps the blends leave. ----
+	if (a->grad_multicast_delta != 0 && !a->accumulate) return E3_ERR_BAD_ARGUMENT;   // the caller zeroes and fences (see header)
 	if (!a->accumulate) {
 		const size_t P = (size_t)a->P;
 		E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), main_st));
@@ -475,7 +479,7 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 				a->raw_rotations, v.viewmatrix, v.projmatrix, v.cam_pos, v.tan_fovx, v.tan_fovy, v.radii, v.geometry_buffer,
 				v.binning_buffer, v.image_buffer, v.seed, 1, a->d_xyz, a->d_features_dc,
 				a->d_features_rest, a->d_opacity_logits, a->d_log_scales, a->d_raw_rotations, k == 0 ? a->d_mean2D : nullptr, 0,
-				sts[k]);
+				sts[k], a->grad_multicast_delta);
 			if (rc) return rc;
 		}
 	}

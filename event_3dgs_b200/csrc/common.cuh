@@ -124,6 +124,9 @@ extern unsigned long long g_e3_launches;
 struct E3Frame {
 	int P, D, M, C, W, H, gx, gy;
 	float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+	// != 0: byte offset from a gradient pointer to its NVLS multicast alias; accumulating gradient
+	// writes then go out as multimem.red (reduced into every rank's copy by the NVSwitch)
+	long long mc_delta = 0;
 };
 
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,

@@ -1,0 +1,83 @@
+// Multi-GPU helper of the fused gradient exchange. sm_100a, NVLink 5 / NVSwitch (NVLS multicast).
+//
+// The reference is single-GPU (utils/general_utils.py:133 pins cuda:0); SURVEY.md 8e defines the
+// exchange of the replicated trainer: the SUM of the parameter gradients over the ranks. With the
+// gradient buffer in symmetric memory and its multicast alias known, the gradient accumulation
+// kernels issue their reductions as multimem.red (preprocess.cu, red_add1 / red_add4), so the
+// all-reduce happens inside the producing kernel and in the switch. This file holds the same
+// operation for small vectors that are not produced by those kernels (the gradient of the event
+// threshold c).
+#include "common.cuh"
+#include "../../include/event3dgs.h"
+
+namespace {
+
+__global__ void multimem_add_kernel(float* __restrict__ mc_dst, const float* __restrict__ src, size_t n, float scale)
+{
+	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+		const float v = src[i] * scale;
+		if (v != 0.f) asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" :: "l"(mc_dst + i), "f"(v) : "memory");
+	}
+}
+
+// In-switch all-reduce of a symmetric buffer through its multicast alias. Every rank owns 1/world of the
+// 16-byte vectors: multimem.ld_reduce (LDGMC.E.ADD.F32x4) fetches the SUM of that vector over all ranks'
+// copies, reduced inside the NVSwitch, and multimem.st writes scale * sum back into every copy. Per GPU
+// this moves n/world in and n/world out plus (world-1) * n/world of incoming broadcasts, against
+// 2 * n * (world-1)/world for a ring. The caller places a cross-rank barrier before (all local
+// accumulation finished) and after (all copies written).
+__device__ __forceinline__ float4 mc_ld_reduce(const float4* p)
+{
+	float4 v;
+	asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+		: "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void mc_st(float4* p, float4 v, float scale)
+{
+	asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(v.x * scale), "f"(v.y * scale),
+		"f"(v.z * scale), "f"(v.w * scale) : "memory");
+}
+
+__global__ void __launch_bounds__(512) nvls_allreduce_kernel(float4* __restrict__ mc, size_t v_begin, size_t v_end, float scale)
+{
+	// four independent in-switch reductions in flight per thread before the first store
+	const size_t stride = (size_t)gridDim.x * blockDim.x;
+	size_t i = v_begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	for (; i + 3 * stride < v_end; i += 4 * stride) {
+		const float4 a = mc_ld_reduce(mc + i), b = mc_ld_reduce(mc + i + stride), c = mc_ld_reduce(mc + i + 2 * stride),
+			d = mc_ld_reduce(mc + i + 3 * stride);
+		mc_st(mc + i, a, scale); mc_st(mc + i + stride, b, scale); mc_st(mc + i + 2 * stride, c, scale); mc_st(mc + i + 3 * stride, d, scale);
+	}
+	for (; i < v_end; i += stride) mc_st(mc + i, mc_ld_reduce(mc + i), scale);
+}
+
+}  // namespace
+
+extern "C" int e3_nvls_allreduce(float* multicast_ptr, size_t n, int rank, int world, float scale, void* stream)
+{
+	if (world < 1 || rank < 0 || rank >= world || (n & 3) || (reinterpret_cast<size_t>(multicast_ptr) & 15)) return E3_ERR_BAD_ARGUMENT;
+	if (n == 0) return 0;
+	if (!multicast_ptr) return E3_ERR_BAD_ARGUMENT;
+	const size_t nv = n / 4;
+	const size_t per = (nv + world - 1) / world;
+	const size_t b = per * (size_t)rank < nv ? per * (size_t)rank : nv;
+	const size_t e = b + per < nv ? b + per : nv;
+	if (e > b) {
+		const size_t want = (e - b + 511) / 512;
+		const unsigned blocks = (unsigned)(want < 148 * 4 ? want : 148 * 4);
+		nvls_allreduce_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_ptr), b, e, scale);
+		g_e3_launches += 1;
+	}
+	return (int)cudaGetLastError();
+}
+
+extern "C" int e3_multimem_add(float* multicast_dst, const float* src, size_t n, float scale, void* stream)
+{
+	if (n == 0) return 0;
+	if (!multicast_dst || !src) return E3_ERR_BAD_ARGUMENT;
+	const unsigned blocks = (unsigned)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+	multimem_add_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(multicast_dst, src, n, scale);
+	g_e3_launches += 1;
+	return (int)cudaGetLastError();
+}

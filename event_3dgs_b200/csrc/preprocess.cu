@@ -411,20 +411,31 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 	dmean.z += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
 }
 
-template <bool ACC>
-__device__ __forceinline__ void put(float* p, float v) { if (ACC) atomicAdd(p, v); else *p = v; }
-
-// 16-byte vector reduction into global memory (REDG.E.ADD.F32x4): accumulation without a read
-// round trip, and safe against the other views' kernels accumulating into the same rows concurrently
-__device__ __forceinline__ void red_add4(float4* p, const float4 v)
+// Accumulating writes. mc == 0: reductions into this GPU's memory (REDG, no read round trip; safe
+// against the other views' kernels accumulating into the same rows concurrently). mc != 0: the same
+// reduction issued on the NVLS multicast alias of the address (multimem.red): the NVSwitch applies it
+// to every rank's copy of the gradient buffer, i.e. the gradient all-reduce happens in this kernel.
+__device__ __forceinline__ void red_add1(float* p, float v, long long mc)
 {
-	asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+	if (mc) asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" :: "l"(reinterpret_cast<char*>(p) + mc), "f"(v) : "memory");
+	else atomicAdd(p, v);
 }
+__device__ __forceinline__ void red_add4(float4* p, const float4 v, long long mc)
+{
+	if (mc)
+		asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(reinterpret_cast<char*>(p) + mc), "f"(v.x),
+			"f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+	else
+		asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <bool ACC>
+__device__ __forceinline__ void put(float* p, float v, long long mc) { if (ACC) red_add1(p, v, mc); else *p = v; }
 
 // coalesced write-out of a staged [rows,K] tile (float4 where the global row start is aligned).
 // ACC: atomic accumulation (all-zero vectors, e.g. the rows of culled Gaussians, are skipped).
 template <bool ACC>
-__device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float* sm, int nfl)
+__device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float* sm, int nfl, long long mc = 0)
 {
 	if ((reinterpret_cast<size_t>(dst) & 15) == 0) {
 		const int nv = nfl >> 2;
@@ -432,12 +443,12 @@ __device__ __forceinline__ void flush_rows(float* __restrict__ dst, const float*
 		const float4* s4 = reinterpret_cast<const float4*>(sm);
 		for (int i = threadIdx.x; i < nv; i += blockDim.x) {
 			const float4 v = s4[i];
-			if (ACC) { if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add4(d4 + i, v); }
+			if (ACC) { if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add4(d4 + i, v, mc); }
 			else d4[i] = v;
 		}
-		for (int i = (nv << 2) + threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) atomicAdd(dst + i, sm[i]); } else dst[i] = sm[i]; }
+		for (int i = (nv << 2) + threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) red_add1(dst + i, sm[i], mc); } else dst[i] = sm[i]; }
 	} else {
-		for (int i = threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) atomicAdd(dst + i, sm[i]); } else dst[i] = sm[i]; }
+		for (int i = threadIdx.x; i < nfl; i += blockDim.x) { if (ACC) { if (sm[i] != 0.f) red_add1(dst + i, sm[i], mc); } else dst[i] = sm[i]; }
 	}
 }
 
@@ -466,7 +477,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	float tan_fovx, float tan_fovy, float* __restrict__ acc,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
-	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot, long long mc)
 {
 	constexpr int BT = E3_PB_THREADS;
 	extern __shared__ __align__(16) float smem[];
@@ -538,7 +549,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 			// sigmoid backward (gaussian_model.py:31): d logit = d opacity * o * (1 - o)
 			float dlogit = 0.f;
 			if (vis) { const float o = 1.0f / (1.0f + expf(-opac_raw)); dlogit = a1.y * o * (1.0f - o); }
-			if (!ACC || vis) put<ACC>(dL_dopacity + idx, dlogit);
+			if (!ACC || vis) put<ACC>(dL_dopacity + idx, dlogit, mc);
 		}
 	}
 	s_cov[3 * t] = a0.x; s_cov[3 * t + 1] = a0.y; s_cov[3 * t + 2] = 0.f;      // d mean2D row
@@ -694,15 +705,15 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 		s_scl[3 * t] = ds[0]; s_scl[3 * t + 1] = ds[1]; s_scl[3 * t + 2] = ds[2];
 		if (live && (!ACC || vis)) {
 			float4* dr = reinterpret_cast<float4*>(dL_drot) + idx;
-			if (ACC) red_add4(dr, dq); else *dr = dq;
+			if (ACC) red_add4(dr, dq, mc); else *dr = dq;
 		}
 	}
 	__syncthreads();
-	flush_rows<ACC>(dL_dmean3D + first * 3, s_mean, rows * 3);
-	if (scales) flush_rows<ACC>(dL_dscale + first * 3, s_scl, rows * 3);
-	if (RAW) flush_rows<ACC>(dL_dsh + first * 3, s_fdc, rows * 3);
+	flush_rows<ACC>(dL_dmean3D + first * 3, s_mean, rows * 3, mc);
+	if (scales) flush_rows<ACC>(dL_dscale + first * 3, s_scl, rows * 3, mc);
+	if (RAW) flush_rows<ACC>(dL_dsh + first * 3, s_fdc, rows * 3, mc);
 	if (dL_dmean2D) flush_rows<false>(dL_dmean2D + first * 3, s_cov, rows * 3);   // this view's own screen-space gradient: assigned
-	if (SHREST) flush_rows<ACC>(d_frest + first * 45, s_dsh, rows * 45);
+	if (SHREST) flush_rows<ACC>(d_frest + first * 45, s_dsh, rows * 45, mc);
 }
 
 }  // namespace
@@ -764,7 +775,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	kern<<<grid, BT, sm, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
-	dL_dscale, dL_drot); } while (0)
+	dL_dscale, dL_drot, (AC) ? f.mc_delta : 0ll); } while (0)
 	if (raw && f.C == 1) {
 		if (shrest) { if (accumulate) LAUNCH(1, true, true, true); else LAUNCH(1, true, false, true); }
 		else { if (accumulate) LAUNCH(1, true, true, false); else LAUNCH(1, true, false, false); }

@@ -142,7 +142,7 @@ def densify_and_prune(pc, optimizer, state, max_grad, min_opacity, extent, max_s
             setattr(pc, attr, newp)
         state.reset(rows, dev)
         # everything sized by P belongs to the old model
-        for stale in ("_grad_flat", "_grad_views", "_e3_ws"):
+        for stale in ("_grad_flat", "_grad_views", "_e3_ws", "_grad_exchange"):
             if hasattr(pc, stale):
                 setattr(pc, stale, None)
     return {"kept": kept, "cloned": cloned, "children_per_draw": children, "split_selected": selected, "rows": rows}

@@ -323,7 +323,18 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
     for f in frames:
         if f.dtype != (torch.uint8 if u8 else torch.float32) or not f.is_contiguous() or tuple(f.shape) != (3, H, W) or f.device != dev:
             raise RuntimeError("event_3dgs_b200.fused: GT frames must be contiguous [3,H,W] on the model's device, all float32 or all uint8")
-    grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D)
+    ex = getattr(pc, "_grad_exchange", None)        # parallel.FusedGradientExchange of the multi-GPU trainer, or None
+    mc = ex if (ex is not None and ex.mode == "push") else None
+    if mc is not None:
+        if not accumulate:
+            mc.begin()                                # zero my copy; barrier: every rank's copy is zeroed
+            grads = _alloc_grads(pc, c, D, flat=mc.buf)
+        else:
+            grads = pc._grad_views
+    elif ex is not None:                              # "pull": accumulate locally, but in the symmetric buffer
+        grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D, flat=ex.buf)
+    else:
+        grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D)
     chans = (3, ec, ec)
     colors = [torch.empty(ch, H, W, dtype=torch.float32, device=dev) for ch in chans]
     radii = [torch.empty(P, dtype=torch.int32, device=dev) for _ in range(3)]
@@ -331,7 +342,9 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
     d_mean2D = None if accumulate else torch.empty_like(pc._xyz)
     a = ws.args
     a.P, a.active_sh_degree, a.width, a.height = P, D, W, H
-    a.binning_capacity, a.scale_modifier, a.accumulate = ws.cap, 1.0, int(bool(accumulate))
+    a.binning_capacity, a.scale_modifier, a.accumulate = ws.cap, 1.0, int(bool(accumulate) or mc is not None)
+    a.grad_multicast_delta = mc.delta if mc is not None else 0
+    a.loss_upstream = float(getattr(pc, "_grad_scale", 1.0)) if mc is not None else 1.0
     a.background = bg.data_ptr()
     a.xyz, a.features_dc, a.features_rest = pc._xyz.data_ptr(), pc._features_dc.data_ptr(), pc._features_rest.data_ptr()
     a.opacity_logits, a.log_scales, a.raw_rotations = pc._opacity.data_ptr(), pc._scaling.data_ptr(), pc._rotation.data_ptr()
@@ -359,10 +372,19 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
     try:
         Rs = ws.check()
     except Workspace.Overflow:
+        if mc is not None:
+            raise RuntimeError("event_3dgs_b200.fused: workspace overflow during a step whose gradients were already reduced "
+                               "into the other ranks; enlarge the workspace (Workspace.resize) and repeat the optimizer step")
         if accumulate:
             raise RuntimeError("event_3dgs_b200.fused: workspace overflow during an accumulating step; repeat the optimizer step")
         return _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, None, accumulate, ws)
-    if accumulate:
+    if mc is not None:
+        # dL/dc comes from the loss kernel (already scaled by loss_upstream): reduce it into every rank's copy too
+        with torch.cuda.device(dev):
+            _lib.check(L.e3_multimem_add(mc.multicast_ptr_of(grads["c"]), out[1:2].data_ptr(), 1, 1.0, stream.cuda_stream))
+        if accumulate:
+            return out[0]
+    elif accumulate:
         grads["c"].add_(out[1:2])
         return out[0]
     pc._xyz.grad = grads["xyz"]
@@ -371,7 +393,10 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
     pc._opacity.grad = grads["opacity"]
     pc._scaling.grad = grads["scaling"]
     pc._rotation.grad = grads["rotation"]
-    _finish_c_grad(c, grads, out)
+    if mc is not None:
+        c.grad = grads["c"].view(c.shape)
+    else:
+        _finish_c_grad(c, grads, out)
     if return_pkg:
         vsp = torch.zeros_like(pc._xyz)
         vsp.grad = d_mean2D
@@ -419,7 +444,13 @@ def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_
     return out[0]
 
 
-def _alloc_grads(pc, c, D):
+def grad_flat_numel(pc, D):
+    """Elements of the flat gradient buffer _alloc_grads lays out for this model at SH degree D."""
+    ts = [pc._xyz, pc._features_dc, pc._opacity, pc._scaling, pc._rotation] + ([pc._features_rest] if D > 0 else [])
+    return sum((t.numel() + 3) // 4 * 4 for t in ts) + 4
+
+
+def _alloc_grads(pc, c, D, flat=None):
     """All gradients of one iteration live in ONE flat buffer (segments padded to 16 bytes), so that
     the multi-GPU trainer exchanges them with a single NCCL all-reduce (parallel.allreduce_flat);
     the per-parameter tensors handed to .grad are views into it. Left on pc as `_grad_flat`."""
@@ -428,15 +459,22 @@ def _alloc_grads(pc, c, D):
     if D > 0:
         names.append(("features_rest", pc._features_rest))
     sizes = [(t.numel() + 3) // 4 * 4 for _, t in names]
-    flat = torch.empty(sum(sizes) + 4, dtype=torch.float32, device=pc._xyz.device)
+    if flat is None:
+        flat = torch.empty(sum(sizes) + 4, dtype=torch.float32, device=pc._xyz.device)
+        fresh = True
+    else:           # caller-owned (symmetric-memory) buffer, already zeroed
+        if flat.numel() != sum(sizes) + 4:
+            raise RuntimeError("gradient buffer has %d elements, the model needs %d" % (flat.numel(), sum(sizes) + 4))
+        fresh = False
     grads, off = {}, 0
     for (n, t), sz in zip(names, sizes):
         grads[n] = flat[off:off + t.numel()].view(t.shape)
-        if sz != t.numel():
+        if fresh and sz != t.numel():
             flat[off + t.numel():off + sz].zero_()
         off += sz
     grads["c"] = flat[off:off + 1]
-    flat[off + 1:off + 4].zero_()
+    if fresh:
+        flat[off + 1:off + 4].zero_()
     if D == 0:
         grads["features_rest"] = _zeros_like_cached(pc._features_rest)
     pc._grad_flat = flat

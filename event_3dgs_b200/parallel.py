@@ -52,6 +52,87 @@ def allreduce_flat(flat, world=None):
         flat.div_(world)
 
 
+class FusedGradientExchange:
+    """Gradient exchange over NVLink 5 / NVSwitch with our own kernels instead of an NCCL call.
+
+    The flat gradient buffer of fused.py lives in symmetric memory (torch.distributed's
+    _symmetric_memory: plumbing only) that is mapped on every rank together with its NVLS multicast
+    alias. Two modes:
+
+    "pull" (default): the backward pass accumulates locally as on one GPU; allreduce() then runs ONE
+        kernel per rank (e3_nvls_allreduce): each rank fetches the in-switch SUM of its 1/world of the
+        vectors (multimem.ld_reduce) and stores scale * sum into every rank's copy (multimem.st),
+        between two cross-rank barriers.
+    "push": e3_event_iteration is told the offset to the multicast alias (grad_multicast_delta) and
+        its gradient-accumulation kernels reduce every row into ALL ranks' copies with multimem.red
+        while the blends of the other views still run; begin() zeroes and fences first, end() fences.
+        No kernel follows the backward pass, but every view's partial gradient crosses the fabric
+        (3x the bytes, world x the incoming bytes per GPU): measured slower than "pull" and than NCCL
+        (profiles/r1_fused_exchange_*.json); kept as the fused compute+collective variant.
+
+    Raises if the box has no multicast support (then use allreduce_flat)."""
+
+    def __init__(self, numel, device, group=None, mode="pull"):
+        import torch.distributed._symmetric_memory as symm
+        group = group or dist.group.WORLD
+        self.buf = symm.empty(numel, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group)
+        mc = int(self.hdl.multicast_ptr)
+        if mc == 0:
+            raise RuntimeError("FusedGradientExchange: no NVLS multicast support on this system")
+        self.delta = mc - self.buf.data_ptr()
+        self.world, self.rank = int(self.hdl.world_size), int(self.hdl.rank)
+        self.numel = numel
+        self.mode = mode
+        self.device = device
+
+    # ---- push mode ----
+    def begin(self):
+        self.buf.zero_()
+        self.hdl.barrier(channel=0)
+
+    def end(self):
+        self.hdl.barrier(channel=0)
+
+    def multicast_ptr_of(self, tensor):
+        """NVLS alias of a view into the buffer."""
+        return tensor.data_ptr() + self.delta
+
+    # ---- pull mode ----
+    def allreduce(self, scale):
+        """buf <- scale * sum over ranks of buf, on the current stream."""
+        from . import _lib
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        self.hdl.barrier(channel=0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().e3_nvls_allreduce(self.buf.data_ptr() + self.delta, self.numel, self.rank, self.world, float(scale), st))
+        self.hdl.barrier(channel=0)
+
+
+_EXCHANGE_UNAVAILABLE = False
+
+
+def fused_exchange_for(pc, numel, device, mode="pull"):
+    """The FusedGradientExchange matching the model's current gradient layout, created collectively
+    (every rank must call this in the same step) when the model changed size; None when the process
+    group has one rank or the system has no NVLS multicast."""
+    global _EXCHANGE_UNAVAILABLE
+    if _EXCHANGE_UNAVAILABLE or not dist.is_initialized() or dist.get_world_size() == 1 or dist.get_backend() != "nccl":
+        return None
+    ex = getattr(pc, "_grad_exchange_cache", None)
+    if ex is not None and ex.numel == numel and ex.mode == mode:
+        return ex
+    pc._grad_exchange_cache = None
+    try:
+        ex = FusedGradientExchange(numel, device, mode=mode)
+    except Exception:
+        _EXCHANGE_UNAVAILABLE = True          # same outcome on every rank of a homogeneous box
+        return None
+    pc._grad_exchange_cache = ex
+    return ex
+
+
 def allreduce_densification_stats(grad_norm_increment, denom_increment, max_radii2D):
     """In-place: SUM of the two accumulator increments, MAX of the screen radii."""
     if not dist.is_initialized() or dist.get_world_size() == 1:

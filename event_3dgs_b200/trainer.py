@@ -80,13 +80,15 @@ class Trainer:
     otherwise one [3,H,W] frame."""
 
     def __init__(self, pc, cams_train, cams_event, gt_for, opt=None, event=True, gray=True, deblur=False, extent=1.0,
-                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1):
+                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True):
         self.pc, self.cams_train, self.cams_event, self.gt_for = pc, cams_train, cams_event, gt_for
         self.opt = opt or optimization_defaults()
         self.event, self.gray, self.deblur = event, gray, deblur
         self.extent = float(extent)
         self.white_background = white_background
         self.rank, self.world = rank, world
+        self.fused_exchange = fused_exchange
+        self.last_exchange = "none"
         if pairs_per_step % world:
             raise ValueError("pairs_per_step must be a multiple of the number of ranks")
         self.pairs_per_step = pairs_per_step
@@ -122,6 +124,14 @@ class Trainer:
         indices = [pick_index(self.rng, n_views, self.event) for _ in range(self.pairs_per_step)]
         bg = torch.rand(3, device=self.dev) if opt.random_background else self.bg
         loss_sum, pkg0 = None, None
+        # gradient exchange fused into the backward kernels (parallel.FusedGradientExchange) whenever the
+        # no-sync workspace path is active on this model; otherwise local accumulation + one NCCL all-reduce
+        exchange = None
+        if self.world > 1 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[0]]) is not None:
+            exchange = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), self.dev,
+                                                   mode=self.fused_exchange if isinstance(self.fused_exchange, str) else "pull")
+        pc._grad_exchange = exchange
+        pc._grad_scale = 1.0 / self.pairs_per_step
         for k, b in enumerate(self.my_pairs):
             index = indices[b]
             if self.event:
@@ -138,10 +148,16 @@ class Trainer:
             else:
                 loss = r
             loss_sum = loss if loss_sum is None else loss_sum + loss
-        if len(self.my_pairs) > 1:
-            pc._grad_flat.div_(len(self.my_pairs))
-        if self.world > 1:
-            parallel.allreduce_flat(pc._grad_flat, self.world)
+        if exchange is not None and exchange.mode == "push":
+            exchange.end()                      # barrier: every rank's reductions have landed in every copy
+        elif exchange is not None:
+            exchange.allreduce(1.0 / self.pairs_per_step)     # one in-switch all-reduce kernel, mean over all pairs
+        else:
+            if len(self.my_pairs) > 1:
+                pc._grad_flat.div_(len(self.my_pairs))
+            if self.world > 1:
+                parallel.allreduce_flat(pc._grad_flat, self.world)
+        self.last_exchange = ("nvls " + exchange.mode) if exchange is not None else ("nccl all-reduce" if self.world > 1 else "none")
         self.last = {"loss": loss_sum / len(self.my_pairs), "indices": indices, "num_rendered": pkg0["num_rendered"]}
 
         if it < opt.densify_until_iter:                        # train.py:317-327

@@ -288,6 +288,20 @@ E3_API int e3_densify_apply(int P, int P_new, int num_split_selected, const e3_d
 E3_API int e3_reset_opacity(int P, float* opacity, float* exp_avg, float* exp_avg_sq, float max_opacity,
 	void* stream);
 
+/* dst[i] += scale * src[i] on every rank at once: multicast_dst is the NVLS multicast alias of a
+ * symmetric-memory buffer (see e3_event_iteration_args.grad_multicast_delta), src is local. Used for
+ * the gradient of the event threshold c, which the loss kernel produces. No counterpart in the
+ * (single-GPU) reference. */
+E3_API int e3_multimem_add(float* multicast_dst, const float* src, size_t n, float scale, void* stream);
+
+/* Gradient all-reduce of the replicated multi-GPU trainer (no counterpart in the
+ * single-GPU reference) as ONE kernel per rank over NVLink 5 / NVSwitch: multicast_ptr is the NVLS
+ * multicast alias of a buffer of n floats (n % 4 == 0) that exists in symmetric memory on all `world`
+ * ranks. Rank r reduces its 1/world of the buffer inside the switch (multimem.ld_reduce) and writes
+ * scale * sum into every rank's copy (multimem.st). The caller issues a cross-rank barrier on the
+ * stream before (local gradients complete everywhere) and after (result complete everywhere). */
+E3_API int e3_nvls_allreduce(float* multicast_ptr, size_t n, int rank, int world, float scale, void* stream);
+
 /* L1 + SSIM loss of the two non-event training branches, value and backward seed:
  * loss = (1 - lambda_dssim) * L1 + lambda_dssim * (1 - SSIM), with the 11x11 Gaussian-window SSIM
  * of utils/loss_utils.py:359-418 (sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2).
@@ -347,6 +361,16 @@ typedef struct e3_event_iteration_args {
 	                                upload of the GT frames on another stream, which then overlaps the renders) */
 	void* forwards_done_event;   /* optional cudaEvent_t, recorded after the third forward: waiting on it
 	                                makes the three num_rendered read-backs visible without draining the stream */
+	float loss_upstream;         /* factor on the loss gradient (0 is read as 1): 1 / (view pairs of the optimizer
+	                                step) makes the accumulated gradient the one of the MEAN loss */
+	long long grad_multicast_delta; /* 0, or the byte offset from each d_* pointer (d_mean2D excepted) to its
+	                                NVLS multicast alias: the gradient tensors then live in symmetric memory
+	                                mapped on every rank, and the accumulation kernels reduce into ALL ranks'
+	                                copies with multimem.red, i.e. the gradient all-reduce of the replicated
+	                                multi-GPU trainer (the reference has none) happens inside
+	                                them. Requires accumulate != 0: the caller zeroes its copy, passes a
+	                                cross-rank barrier, runs the iteration(s), passes a second barrier, and
+	                                then holds the sum over all ranks. */
 } e3_event_iteration_args;
 E3_API int e3_event_iteration(const e3_event_iteration_args* args_host, void* stream);
 
