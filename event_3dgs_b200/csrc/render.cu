@@ -254,6 +254,9 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 	float last_alpha = 0.f;
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask), aId = smem_addr(sId);
+	// after warp_reduce8 lane L with (L & 3) == 0 holds slot my_slot of the accumulator row
+	const int my_slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+	const float slot_scale = my_slot == 0 ? ddelx_dx : my_slot == 1 ? ddely_dy : my_slot < 5 ? -0.5f : 1.0f;
 
 	// instance index within the tile's list, walked from total-1 down to 0; an instance with
 	// 0-based index i has contributor number i (reference: `contributor--` before the test,
@@ -326,11 +329,13 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const float gdx = G * dx, gdy = G * dy;
 			const float dG_ddelx = -gdx * a.z - gdy * a.w;
 			const float dG_ddely = -gdy * b.x - gdx * a.w;
-			v[0] = dL_dG * dG_ddelx * ddelx_dx;
-			v[1] = dL_dG * dG_ddely * ddely_dy;
-			v[2] = -0.5f * gdx * dx * dL_dG;
-			v[3] = -0.5f * gdx * dy * dL_dG;
-			v[4] = -0.5f * gdy * dy * dL_dG;
+			// the constant factors (0.5 W, 0.5 H on the mean, -0.5 on the conic) are applied once, after the
+			// warp reduction, by the lane that writes the slot (slot_scale)
+			v[0] = dL_dG * dG_ddelx;
+			v[1] = dL_dG * dG_ddely;
+			v[2] = gdx * dx * dL_dG;
+			v[3] = gdx * dy * dL_dG;
+			v[4] = gdy * dy * dL_dG;
 			v[5] = G * dL_dalpha;
 			v[6] = dchannel_dcolor * dL_dpixel[0];
 			v[7] = 0.f;
@@ -342,8 +347,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			}
 			if ((lane & 3) == 0) {
 				float* dst = acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE;
-				const int slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-				if (C == 3 || slot < 7) atomicAdd(dst + slot, v[0]);
+				if (C == 3 || my_slot < 7) atomicAdd(dst + my_slot, v[0] * slot_scale);
 			}
 			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + 8, v8);
 		}
