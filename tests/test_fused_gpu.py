@@ -278,3 +278,62 @@ def test_no_sync_workspace_path_and_overflow_recovery(cuda_dev):
     assert torch.equal(pc_pkg["render"], img_a)
     for p, a in zip(leaves, ga):
         assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+
+
+def _fused_vs_dropin(pl, pc, cams, gt, bg, c, calls=2, tol=3e-4):
+    """Both calls of the fused path (the workspace-sizing one and the no-sync single call) against autograd."""
+    from event_3dgs_b200 import fused
+    leaves = pc.leaves() + [c]
+    for p in leaves:
+        p.grad = None
+    la, _ = pl.event_iteration(pc, cams[1], cams[1], cams[2], gt, c, bg)
+    la.backward()
+    ga = [p.grad.clone() for p in leaves]
+    for k in range(calls):
+        for p in leaves:
+            p.grad = None
+        lb = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
+        assert abs(la.item() - lb.item()) <= 1e-5 * max(abs(la.item()), 1e-6), k
+        for a, p in zip(ga, leaves):
+            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-12) < tol, k
+
+
+def test_fused_edge_cases(cuda_dev):
+    """Ragged image sizes, splats larger than 32 tiles, nothing visible, a single Gaussian, no Gaussian."""
+    from event_3dgs_b200 import fused
+    # image not a multiple of the tile, fewer pixels than one tile in one direction
+    for (W, H) in ((100, 37), (17, 9), (16, 16)):
+        pl, pc, cams, gt, bg, c = _setup(3_000, W, H, 0, False, seed=2)
+        _fused_vs_dropin(pl, pc, cams, gt, bg, c)
+    # huge splats: every Gaussian covers (much) more than 32 tiles -> cooperative emission, long tile lists
+    pl, pc, cams, gt, bg, c = _setup(400, 200, 120, 0, False, seed=3)
+    with torch.no_grad():
+        pc._scaling.add_(2.5)
+    _fused_vs_dropin(pl, pc, cams, gt, bg, c)
+    assert pc._e3_ws is not None
+    # nothing visible: all Gaussians behind the camera -> R = 0, image = background, zero gradients
+    pl, pc, cams, gt, bg, c = _setup(2_000, 64, 48, 0, False, seed=4)
+    with torch.no_grad():
+        pc._xyz.mul_(0.01)
+        pc._xyz.add_(torch.as_tensor(cams[1].camera_center) * 3.0)      # three camera distances beyond the camera
+    for k in range(2):
+        loss, pkg = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg, return_pkg=True)
+        assert pkg["num_rendered"][0] == 0 and not pkg["visibility_filter"].any()
+        assert torch.isfinite(loss) and not pc._xyz.grad.any() and not pc._opacity.grad.any()
+    # one Gaussian
+    pl, pc, cams, gt, bg, c = _setup(1, 64, 48, 0, False, seed=5)
+    with torch.no_grad():
+        pc._xyz.zero_()
+        pc._scaling.copy_(torch.tensor([[-1.5, -2.2, -1.0]]))      # anisotropic: dL/drotation is not identically zero
+        pc._opacity.fill_(2.0)
+    _fused_vs_dropin(pl, pc, cams, gt, bg, c)
+    # no Gaussian at all: rasterize_points.cu:81 -> all-zero image; the loss is still defined
+    pl, pc, cams, gt, bg, c = _setup(1, 64, 48, 0, False, seed=6)
+    pc._xyz = torch.nn.Parameter(pc._xyz[:0].contiguous())
+    pc._features_dc = torch.nn.Parameter(pc._features_dc[:0].contiguous())
+    pc._features_rest = torch.nn.Parameter(pc._features_rest[:0].contiguous())
+    pc._scaling = torch.nn.Parameter(pc._scaling[:0].contiguous())
+    pc._rotation = torch.nn.Parameter(pc._rotation[:0].contiguous())
+    pc._opacity = torch.nn.Parameter(pc._opacity[:0].contiguous())
+    loss = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
+    assert torch.isfinite(loss) and pc._xyz.grad.shape == (0, 3)
