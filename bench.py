@@ -529,6 +529,18 @@ def main():
                               "what": "iteration + densification statistics + fused Adam (6 groups) + Adam(c), one view-pair per step"}
         del trn, pc_t
 
+    if use_fused and world == 1:
+        # extra: the non-event branch of train.py (one render, L1 + SSIM on the luma, :213-223) through
+        # fused.frame_iteration_backward (fused SSIM kernel, no-sync workspace)
+        def it_frame(s):
+            v = view_of(args.warmup + s)
+            fused.frame_iteration_backward(pc, cams[v], gt_dev["intensity"], bg, 0.2, True)
+        for s in range(3):
+            it_frame(s)
+        ms_f, _, _ = timed(it_frame, args.steps)
+        line["frame_mode_gray"] = {"value": 1e3 / (ms_f / args.steps), "unit": UNIT, "ms_per_step": ms_f / args.steps,
+                                   "what": "1 render fwd + 0.8 L1 + 0.2 (1 - SSIM) on the luma + bwd (train.py --gray without --event)"}
+
     if rank == 0 and world == 1:
         # reference CUDA build (oracle/_ref) on the same tensors, same timing window
         if not args.no_ref_cuda:
@@ -605,6 +617,18 @@ def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves
             opt_c.step()
             opt_c.zero_grad(set_to_none=True)
 
+    def frame_it(s):
+        v = view_of(args.warmup + s)
+        for p in leaves:
+            p.grad = None
+        pkg = render_ref(cams[v], pc, pl.PIPE, bg)
+        pl.l1_ssim_loss(pkg["render"], gt["intensity"].float() if gt["intensity"].dtype != torch.float32 else gt["intensity"], 0.2, True).backward()
+
+    for s in range(3):
+        frame_it(s)
+    ms_f, _, _ = timed(frame_it, steps)
+    out["frame_mode_gray"] = {"value": 1e3 / (ms_f / steps), "unit": UNIT, "ms_per_step": ms_f / steps,
+                              "what": "reference rasterizer + PyTorch SH / L1 / 5-conv SSIM (utils/loss_utils.py:368-385) + autograd"}
     for s in range(3):
         train_it(s)
     ms_t, _, _ = timed(train_it, steps)

@@ -523,11 +523,16 @@ def l1_ssim_loss_and_seed(image, gt_image, lambda_dssim=0.2, gray=False, upstrea
     return out, seed
 
 
-def frame_iteration_backward(pc, cam, gt_image, bg, lambda_dssim=0.2, gray=False, return_pkg=False):
+def frame_iteration_backward(pc, cam, gt_image, bg, lambda_dssim=0.2, gray=False, return_pkg=False, no_sync=True):
     """The non-event iteration of train.py (one render, L1 + SSIM loss, loss.backward()): the
     --gray branch (:213-223) with gray=True, the RGB branch (:292-296) with gray=False. Sets .grad
     on the six leaf tensors of pc and returns the loss."""
-    st = _forward_raw(pc, cam, bg)
+    # after the first call (which reads num_rendered back and sizes a persistent Workspace) nothing
+    # blocks the host any more, exactly as in event_iteration_backward
+    ws = _workspace_for(pc, cam) if (no_sync and pc._xyz.shape[0] > 0) else None
+    st = _forward_raw(pc, cam, bg, ws=ws, slot=0)
+    if ws is None and no_sync and pc._xyz.shape[0] > 0:
+        _remember_workspace(pc, cam, st.R)
     out, seed = l1_ssim_loss_and_seed(st.color, gt_image, lambda_dssim, gray)
     D = int(pc.active_sh_degree)
     dummy_c = torch.zeros(1, device=pc._xyz.device)
@@ -535,6 +540,11 @@ def frame_iteration_backward(pc, cam, gt_image, bg, lambda_dssim=0.2, gray=False
     d_mean2D = torch.empty_like(pc._xyz)
     _backward_raw(pc, st, bg, seed, grads, False, d_mean2D)
     grads["c"].zero_()
+    if ws is not None:
+        try:
+            st.R = ws.check()[0]
+        except Workspace.Overflow:      # more instances than the workspace holds: it has been enlarged, redo the step
+            return frame_iteration_backward(pc, cam, gt_image, bg, lambda_dssim, gray, return_pkg, no_sync)
     pc._xyz.grad = grads["xyz"]
     pc._features_dc.grad = grads["features_dc"]
     pc._features_rest.grad = grads["features_rest"]
