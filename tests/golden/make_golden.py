@@ -90,6 +90,27 @@ def sh_case(seed, P):
     return out
 
 
+def schedule_golden():
+    """tests/golden/schedule.json: the learning-rate schedule (utils/general_utils.py:38-62, called by
+    the reference itself) and the view-index sequence of train.py:123-139 under random.seed(0)."""
+    import json
+    import random
+    from utils.general_utils import get_expon_lr_func
+    f = get_expon_lr_func(lr_init=0.00016 * 2.6, lr_final=0.0000016 * 2.6, lr_delay_mult=0.01, max_steps=30000)
+    g_ = get_expon_lr_func(lr_init=0.01, lr_final=0.0001, lr_delay_steps=500, lr_delay_mult=0.05, max_steps=2000)
+    steps = [0, 1, 2, 10, 100, 999, 1000, 5000, 15000, 29999, 30000, 40000]
+
+    def pick(n, event):
+        index = random.randint(2, n - 4) if event else random.randint(2, n - 3)
+        return index - 1 if index in (5, 25, 45, 65, 85) else index
+    random.seed(0)
+    ev = [pick(96, True) for _ in range(40)]
+    random.seed(0)
+    fr = [pick(96, False) for _ in range(40)]
+    json.dump({"steps": steps, "lr_xyz": [float(f(s)) for s in steps], "lr_delay": [float(g_(s)) for s in steps],
+               "views_event": ev, "views_frame": fr}, open(os.path.join(HERE, "schedule.json"), "w"), indent=1)
+
+
 if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "event_loss_a.npz"), **event_case(0, 24, 40, False, 0.7))
     np.savez_compressed(os.path.join(HERE, "event_loss_b.npz"), **event_case(1, 17, 33, True, 0.3))
@@ -97,4 +118,6 @@ if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "eval_sh.npz"), **sh_case(3, 64))
     np.savez_compressed(os.path.join(HERE, "l1_ssim_gray.npz"), **ssim_case(4, 37, 50, True))
     np.savez_compressed(os.path.join(HERE, "l1_ssim_rgb.npz"), **ssim_case(5, 33, 20, False))
+    schedule_golden()
     print("golden vectors written to", HERE)
+
