@@ -27,7 +27,9 @@ static inline void e3_carve(char*& p, T*& out, size_t count)
 
 // Radix-sort scratch: `counts` holds one digit histogram per sort block.
 #define E3_SORT_THREADS 256
+#ifndef E3_SORT_ITEMS
 #define E3_SORT_ITEMS 16
+#endif
 #define E3_SORT_TILE (E3_SORT_THREADS * E3_SORT_ITEMS)
 #define E3_SCAN_THREADS 256
 #define E3_SCAN_ITEMS 8
