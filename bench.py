@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--pairs", type=int, default=None,
                     help="event view-pairs per optimizer step over all ranks (default: one per rank; c5: 64)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "nccl"],
-                    help="multi-GPU gradient exchange: auto = own NVLS all-reduce kernel when the box supports multicast, else NCCL")
+                    help="multi-GPU gradient exchange: auto = own NVLS all-reduce kernel from 4 GPUs on when the box supports multicast, else NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=25.0)
@@ -289,7 +289,7 @@ def main():
             p.grad = None
         loss = None
         ex = None
-        if world > 1 and use_fused and args.exchange != "nccl" and fused._workspace_for(pc, cams[view_of(step, my_pairs[0])]) is not None:
+        if world >= 4 and use_fused and args.exchange != "nccl" and fused._workspace_for(pc, cams[view_of(step, my_pairs[0])]) is not None:
             # our own in-switch all-reduce kernel over the NVLS multicast alias of the gradient buffer
             # (parallel.FusedGradientExchange, e3_nvls_allreduce); NCCL when the box has no multicast
             ex = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), dev)
@@ -350,7 +350,9 @@ def main():
         iteration(s, gt_dev)
     torch.cuda.synchronize()
 
-    if world > 1 and use_fused and args.exchange == "auto":
+    if world >= 4 and use_fused and args.exchange == "auto":
+        # (at 2 GPUs NCCL's peer-to-peer path moves 2/3 of the bytes of the in-switch one and is 0.06 ms faster:
+        # profiles/r1_exchange_alone_n2.json; from 4 GPUs on the in-switch kernel is used)
         # self-check of the in-switch all-reduce against NCCL on the same step (the two runs differ by the
         # run-to-run spread of the float atomics); any rank failing it sends everyone to NCCL
         args.exchange = "nccl"

@@ -39,15 +39,18 @@ __device__ __forceinline__ void mc_st(float4* p, float4 v, float scale)
 		"f"(v.z * scale), "f"(v.w * scale) : "memory");
 }
 
+template <int U>
 __global__ void __launch_bounds__(512) nvls_allreduce_kernel(float4* __restrict__ mc, size_t v_begin, size_t v_end, float scale)
 {
-	// four independent in-switch reductions in flight per thread before the first store
+	// U independent in-switch reductions in flight per thread before the first store
 	const size_t stride = (size_t)gridDim.x * blockDim.x;
 	size_t i = v_begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	for (; i + 3 * stride < v_end; i += 4 * stride) {
-		const float4 a = mc_ld_reduce(mc + i), b = mc_ld_reduce(mc + i + stride), c = mc_ld_reduce(mc + i + 2 * stride),
-			d = mc_ld_reduce(mc + i + 3 * stride);
-		mc_st(mc + i, a, scale); mc_st(mc + i + stride, b, scale); mc_st(mc + i + 2 * stride, c, scale); mc_st(mc + i + 3 * stride, d, scale);
+	for (; i + (U - 1) * stride < v_end; i += U * stride) {
+		float4 v[U];
+#pragma unroll
+		for (int k = 0; k < U; k++) v[k] = mc_ld_reduce(mc + i + k * stride);
+#pragma unroll
+		for (int k = 0; k < U; k++) mc_st(mc + i + k * stride, v[k], scale);
 	}
 	for (; i < v_end; i += stride) mc_st(mc + i, mc_ld_reduce(mc + i), scale);
 }
@@ -64,9 +67,15 @@ extern "C" int e3_nvls_allreduce(float* multicast_ptr, size_t n, int rank, int w
 	const size_t b = per * (size_t)rank < nv ? per * (size_t)rank : nv;
 	const size_t e = b + per < nv ? b + per : nv;
 	if (e > b) {
+		// grid and unroll do not matter between 32..592 blocks and 4..8 vectors in flight per thread: the
+		// kernel runs at what the fabric delivers (profiles/r1_nvls_allreduce_sweep_n2.txt)
+		const int cfg_blocks = 148 * 4, cfg_unroll = 4;
 		const size_t want = (e - b + 511) / 512;
-		const unsigned blocks = (unsigned)(want < 148 * 4 ? want : 148 * 4);
-		nvls_allreduce_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_ptr), b, e, scale);
+		const unsigned blocks = (unsigned)(want < (size_t)cfg_blocks ? want : (size_t)cfg_blocks);
+		float4* p = reinterpret_cast<float4*>(multicast_ptr);
+		if (cfg_unroll >= 8) nvls_allreduce_kernel<8><<<blocks, 512, 0, (cudaStream_t)stream>>>(p, b, e, scale);
+		else if (cfg_unroll >= 4) nvls_allreduce_kernel<4><<<blocks, 512, 0, (cudaStream_t)stream>>>(p, b, e, scale);
+		else nvls_allreduce_kernel<1><<<blocks, 512, 0, (cudaStream_t)stream>>>(p, b, e, scale);
 		g_e3_launches += 1;
 	}
 	return (int)cudaGetLastError();

@@ -127,7 +127,7 @@ class Trainer:
         # gradient exchange fused into the backward kernels (parallel.FusedGradientExchange) whenever the
         # no-sync workspace path is active on this model; otherwise local accumulation + one NCCL all-reduce
         exchange = None
-        if self.world > 1 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[0]]) is not None:
+        if self.world >= 4 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[0]]) is not None:
             exchange = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), self.dev,
                                                    mode=self.fused_exchange if isinstance(self.fused_exchange, str) else "pull")
         pc._grad_exchange = exchange
