@@ -42,6 +42,8 @@ def parse():
                     help="event view-pairs per optimizer step over all ranks (default: one per rank; c5: 64)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "nccl"],
                     help="multi-GPU gradient exchange: auto = own NVLS all-reduce kernel from 4 GPUs on when the box supports multicast, else NCCL")
+    ap.add_argument("--dropin-no-sync", action="store_true",
+                    help="with --path dropin: the opt-in forward without the host read-back of num_rendered (E3_DROPIN_NO_SYNC)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=25.0)
@@ -271,6 +273,10 @@ def main():
             if args.path == "fused":
                 raise
     path_name = "fused" if use_fused else "dropin"
+    if args.dropin_no_sync:
+        from event_3dgs_b200 import rasterizer as _rz
+        _rz.NO_SYNC = True
+        path_name += " (no-sync forward, opt-in)"
 
     from event_3dgs_b200 import parallel
     pairs = args.pairs or (64 if cfg_name == "c5" else world)
@@ -562,6 +568,7 @@ def main():
 
 def last_num_rendered():
     from event_3dgs_b200 import rasterizer
+    rasterizer.verify_no_sync(True)
     return rasterizer.LAST_NUM_RENDERED
 
 

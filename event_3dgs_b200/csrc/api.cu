@@ -260,6 +260,24 @@ int e3_rasterize_forward_raw_ws(
 		raw_rotations, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, 0, out_color, radii, debug, stream, nullptr);
 }
 
+int e3_rasterize_forward_ws(
+	char* geometry_buffer, char* binning_buffer, size_t binning_capacity, char* image_buffer, int* num_rendered_host,
+	int P, int D, int M, int channels,
+	const float* background, int width, int height,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy, int prefiltered,
+	float* out_color, int* radii, int debug, void* stream)
+{
+	if (P > 0 && (!geometry_buffer || !binning_buffer || !image_buffer || !num_rendered_host || binning_capacity == 0))
+		return E3_ERR_BAD_ARGUMENT;
+	WsMode ws = { geometry_buffer, binning_buffer, binning_capacity, image_buffer, num_rendered_host };
+	return forward_impl(&ws, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, P, D, M, channels,
+		background, width, height, means3D, shs, nullptr, false, colors_precomp, opacities, scales, scale_modifier, rotations,
+		cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, out_color, radii, debug, stream, nullptr);
+}
+
 int e3_rasterize_backward(
 	int P, int D, int M, int R, int channels,
 	const float* background, int width, int height,

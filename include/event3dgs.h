@@ -150,6 +150,23 @@ E3_API int e3_rasterize_forward_raw(
 	float tan_fovx, float tan_fovy,
 	float* out_color, int* radii, int debug, void* stream, int* num_rendered_host);
 
+/* e3_rasterize_forward without the host round trip (see e3_rasterize_forward_raw_ws for the contract:
+ * caller-owned buffers, binning_capacity an estimate of num_rendered, {R, prefiltered flag} copied
+ * asynchronously to num_rendered_host[0..1] in pinned memory, the caller verifies R <=
+ * binning_capacity afterwards). Opt-in route of the drop-in binding (E3_DROPIN_NO_SYNC=1): the
+ * reference's blocking read (cuda_rasterizer/rasterizer_impl.cu:281) is what keeps the host from
+ * running ahead of the ~100 small ATen launches between two renders. For the backward pass hand
+ * e3_rasterize_backward the same buffers and binning_capacity as its R. */
+E3_API int e3_rasterize_forward_ws(
+	char* geometry_buffer, char* binning_buffer, size_t binning_capacity, char* image_buffer, int* num_rendered_host,
+	int P, int D, int M, int channels,
+	const float* background, int width, int height,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+	float tan_fovx, float tan_fovy, int prefiltered,
+	float* out_color, int* radii, int debug, void* stream);
+
 /* e3_rasterize_forward_raw without the host round trip. The reference blocks the host in every
  * forward to read num_rendered and size the binning buffer (cuda_rasterizer/rasterizer_impl.cu:
  * 281-285); at event-camera resolutions (346x260) that stall and the launch gaps around it cost more

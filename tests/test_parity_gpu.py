@@ -357,3 +357,53 @@ def test_full_size_c5_properties(gc):
     ones["bg"] = np.array([1.0, 1.0, 1.0], np.float32)
     fw1 = gc.ours_forward(ones)
     assert float((fw1["color"] - 1.0).abs().max()) < 1e-5
+
+
+def test_dropin_no_sync_forward_matches_and_detects_overflow(gc):
+    """E3_DROPIN_NO_SYNC: after the learning calls the forward no longer reads num_rendered back; results are
+    unchanged, R arrives later, and a render that exceeded its binning buffer is reported."""
+    from event_3dgs_b200 import pipeline as pl
+    from event_3dgs_b200 import rasterizer as rz
+    from event_3dgs_b200 import synthetic as syn
+    dev = torch.device("cuda:0")
+    sc = syn.make_scene(dict(P=20_000, W=200, H=120, sh_degree=1, deblur=False), seed=9)
+    pc = pl.GaussianParams(sc["gaussians"], dev)
+    cams = [pl.make_camera(c, dev) for c in sc["cameras"][:12]]
+    bg = torch.zeros(3, device=dev)
+
+    def run(cam):
+        for p in pc.leaves():
+            p.grad = None
+        pkg = pl.render(cam, pc, pl.PIPE, bg)
+        (pkg["render"] * torch.linspace(0.5, 1.5, 120, device=dev).view(1, 120, 1)).sum().backward()
+        return pkg["render"].detach().clone(), pkg["radii"].clone(), [p.grad.clone() for p in pc.leaves()], pkg["viewspace_points"].grad.clone()
+
+    rz.verify_no_sync(True)
+    ref = [run(c) for c in cams]
+    old = rz.NO_SYNC
+    key = (20_000, 200, 120, dev)
+    try:
+        rz.NO_SYNC = True
+        rz._cap_stats.pop(key, None)
+        for i, c in enumerate(cams):                  # 8 learning calls, then no-sync
+            img, radii, grads, vs = run(c)
+            assert torch.equal(img.view(torch.int32), ref[i][0].view(torch.int32)), i
+            assert torch.equal(radii, ref[i][1])
+            for a, b in zip(grads, ref[i][2]):
+                assert rel_err(_np(a), _np(b), 1e-12) < 1e-4
+            assert rel_err(_np(vs), _np(ref[i][3])) < 1e-4
+        rz.verify_no_sync(True)
+        assert rz._cap_stats[key][0] == len(cams) and rz._cap_stats[key][1] > 0
+        assert rz.LAST_NUM_RENDERED == rz._cap_stats[key][1] or rz.LAST_NUM_RENDERED > 0
+        # overflow: pretend far fewer instances had been seen
+        rz._cap_stats[key][1] = 10
+        run(cams[0])
+        with pytest.raises(RuntimeError, match="incomplete"):
+            rz.verify_no_sync(True)
+        assert rz._cap_stats[key][1] > 10             # learned the real count
+        img, _, _, _ = run(cams[0])                   # and works again
+        rz.verify_no_sync(True)
+        assert torch.equal(img.view(torch.int32), ref[0][0].view(torch.int32))
+    finally:
+        rz.NO_SYNC = old
+        rz._cap_stats.pop(key, None)
