@@ -58,7 +58,7 @@ def test_trainer_steps_match_reference_shaped_loop(cuda_dev):
         d = (a.detach() - b.detach()).abs()
         frac_off = float((d > 0.05 * 5 * max(g["lr"], 1e-12)).float().mean())
         assert frac_off < 2e-3, (g["name"], frac_off)
-    assert abs(float(t.c) - float(c_ref)) < 1e-3
+    assert abs(float(t.c.detach()) - float(c_ref.detach())) < 1e-3
     assert torch.equal(pc._features_rest.detach(), pc_ref._features_rest.detach())
 
 
@@ -92,3 +92,20 @@ def test_training_run_with_densification_and_opacity_reset(cuda_dev):
                     event=False, gray=True, extent=2.6)
     l0 = [float(t2.step()) for _ in range(25)]
     assert all(np.isfinite(l0)) and pc2._xyz.shape[0] != 8_000
+
+
+def test_trainer_dedupe_views_gives_the_same_losses(cuda_dev):
+    """Opt-in dedupe (train camera == first event camera rendered once): same loss values, same parameters
+    up to fp32 summation order after a few steps."""
+    from event_3dgs_b200 import trainer as tr
+    _, pa, cams, gt = scene_on(cuda_dev, P=8_000)
+    _, pb, _, _ = scene_on(cuda_dev, P=8_000)
+    opt = lambda: tr.optimization_defaults(densify_from_iter=10 ** 9)
+    ta = tr.Trainer(pa, cams, cams, lambda i: gt, opt=opt(), event=True, extent=2.6, seed=2)
+    tb = tr.Trainer(pb, cams, cams, lambda i: gt, opt=opt(), event=True, extent=2.6, seed=2, dedupe_views=True)
+    for it in range(6):
+        la, lb = float(ta.step()), float(tb.step())
+        assert abs(la - lb) <= 1e-4 * abs(la), it
+    assert float((pa._features_dc.detach() - pb._features_dc.detach()).abs().max()) < 2e-3
+    with pytest.raises(ValueError):
+        tr.Trainer(pb, cams, cams, lambda i: gt, event=True, pairs_per_step=2, dedupe_views=True)
