@@ -57,7 +57,7 @@ def main(config="c2", P=100_000, steps=60):
                 same = same and bool(torch.equal(a, b))
     if rank == 0:
         print(json.dumps({"world": world, "pairs_per_step": 2 * world, "steps": steps, "rows_start": P, "rows_after_each_densification": sizes,
-                          "replicas_bit_identical": same, "loss_first": float(losses[0]), "loss_last": float(losses[-1]),
+                          "replicas_bit_identical": same, "gradient_exchange": t.last_exchange, "loss_first": float(losses[0]), "loss_last": float(losses[-1]),
                           "pairs_per_sec_incl_densification": 2 * world * steps / dt}))
     if world > 1:
         dist.destroy_process_group()
