@@ -337,3 +337,29 @@ def test_fused_edge_cases(cuda_dev):
     pc._opacity = torch.nn.Parameter(pc._opacity[:0].contiguous())
     loss = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
     assert torch.isfinite(loss) and pc._xyz.grad.shape == (0, 3)
+
+
+def test_tight_instance_lists_do_not_change_the_image(cuda_dev):
+    """The fused path emits instances only for tiles inside the alpha >= 1/255 box; the drop-in path keeps the
+    reference's 3-sigma lists. With unit quaternions the in-kernel activations equal ATen's bit for bit (same expf,
+    same division), so both paths blend the same Gaussians: radii must be identical, the instance count must
+    drop, and the images may differ only by the rounding of the colour evaluation -- a single dropped
+    contribution would show up as >= 1/255 of a colour."""
+    from event_3dgs_b200 import fused
+    for seed, (W, H) in ((1, (346, 260)), (2, (200, 120))):
+        pl, pc, cams, gt, bg, c = _setup(40_000, W, H, 0, False, seed=seed)
+        with torch.no_grad():
+            pc._rotation.zero_()
+            pc._rotation[:, 0] = 1.0
+            pc._opacity.add_(torch.randn_like(pc._opacity))           # many low-opacity Gaussians: small alpha boxes
+        bgc = torch.tensor([0.2, 0.5, 0.7], device=cuda_dev)
+        for cam in cams[:3]:
+            with torch.no_grad():
+                ref = pl.render(cam, pc, pl.PIPE, bgc)
+            from event_3dgs_b200 import rasterizer as rz
+            R_ref = rz.LAST_NUM_RENDERED
+            st = fused._forward_raw(pc, cam, bgc)
+            assert torch.equal(st.radii, ref["radii"])
+            assert 0 < st.R < 0.95 * R_ref, (st.R, R_ref)
+            d = float((st.color - ref["render"]).abs().max())
+            assert d < 3e-6, d
