@@ -520,7 +520,7 @@ def main():
             it_dedupe(s)
         ms_d, _, _ = timed(it_dedupe, args.steps)
         line["dedupe_identical_views"] = {"value": world * 1e3 / (ms_d / args.steps), "unit": UNIT, "ms_per_step": ms_d / args.steps,
-                                          "note": "opt-in; 2 renders instead of 3 when train and event camera coincide; no gradient exchange in this extra"}
+                                          "note": "not the headline: the intensity view and the first event view are the same camera and are rendered once; the backward blend of the shared view carries two seeds, so loss, parameter gradients and the densification statistic equal the three-render iteration (tests); no gradient exchange in this extra"}
 
     if use_fused and world == 1:
         # extra: the whole training step of train.py:95-332 (iteration + densification statistics + both

@@ -96,6 +96,8 @@ SIGNATURES["e3_event_iteration"] = (_i, [ctypes.POINTER(EventIterationArgs), _vp
 SIGNATURES["e3_adam_step"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, _vp])
 SIGNATURES["e3_rasterize_forward_ws"] = (_i, [_vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp,
                                              _vp, _vp, _vp, _f, _f, _i, _vp, _vp, _i, _vp])
+SIGNATURES["e3_rasterize_backward_raw_dual"] = (_i, [_i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
+                                                    _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp])
 SIGNATURES["e3_multimem_add"] = (_i, [_vp, _vp, _sz, _f, _vp])
 SIGNATURES["e3_nvls_allreduce"] = (_i, [_vp, _sz, _i, _i, _f, _vp])
 SIGNATURES["e3_densification_stats"] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp])

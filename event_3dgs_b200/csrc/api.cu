@@ -327,7 +327,7 @@ static int backward_raw_impl(int phase,
 	const float* dL_dpix, int accumulate,
 	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
 	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
-	int debug, void* stream, long long mc_delta = 0)
+	int debug, void* stream, long long mc_delta = 0, const float* dL_dpix_stats = nullptr)
 {
 	cudaStream_t st = (cudaStream_t)stream;
 	if (P < 0 || active_sh_degree < 0 || active_sh_degree > 3 || (channels != 1 && channels != 3)) return E3_ERR_BAD_ARGUMENT;
@@ -340,6 +340,8 @@ static int backward_raw_impl(int phase,
 	if (active_sh_degree > 0 && (!features_rest || !d_features_rest)) return E3_ERR_BAD_ARGUMENT;
 	E3Frame f = make_frame(P, active_sh_degree, 16, channels, width, height, tan_fovx, tan_fovy, scale_modifier);
 	f.mc_delta = mc_delta;
+	if (dL_dpix_stats && (channels != 3 || !d_mean2D)) return E3_ERR_BAD_ARGUMENT;
+	f.mean2d_from_second_seed = dL_dpix_stats != nullptr;
 	const size_t N = (size_t)width * height, T = (size_t)f.gx * f.gy;
 	E3GeomState g = E3GeomState::carve(geometry_buffer, P);
 	E3ImageState im = E3ImageState::carve(image_buffer, N, T);
@@ -347,7 +349,7 @@ static int backward_raw_impl(int phase,
 	if (R > 0 && (phase & 1)) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
 		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib,
-			dL_dpix, g.acc, st));
+			dL_dpix, g.acc, st, dL_dpix_stats));
 	}
 	if (phase & 2)
 		E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, xyz, radii, features_dc, features_rest, opacity_logits, true,
@@ -375,6 +377,25 @@ int e3_rasterize_backward_raw(
 		d_log_scales, d_raw_rotations, d_mean2D, debug, stream);
 }
 
+int e3_rasterize_backward_raw_dual(
+	int P, int active_sh_degree, int channels, int R,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, const float* dL_dpix_stats, int accumulate,
+	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
+	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
+	int debug, void* stream)
+{
+	return backward_raw_impl(3, P, active_sh_degree, channels, R, background, width, height, xyz, features_dc, features_rest,
+		opacity_logits, log_scales, scale_modifier, raw_rotations, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+		geometry_buffer, binning_buffer, image_buffer, dL_dpix, accumulate, d_xyz, d_features_dc, d_features_rest, d_opacity_logits,
+		d_log_scales, d_raw_rotations, d_mean2D, debug, stream, 0, dL_dpix_stats);
+}
+
 int e3_event_loss(int width, int height, const float* image, const float* image_now, const float* image_next,
 	const void* gt_now, const void* gt_next, const void* gt_intensity, const void* gt_blur, int gt_is_u8, const float* c,
 	float upstream, int event_channels, void* scratch, size_t scratch_bytes, float* d_image, float* d_image_now,
@@ -382,7 +403,7 @@ int e3_event_loss(int width, int height, const float* image, const float* image_
 {
 	cudaStream_t st = (cudaStream_t)stream;
 	const int debug = 0;
-	if ((event_channels != 1 && event_channels != 3) || width <= 0 || height <= 0 || !image || !image_now || !image_next || !gt_now || !gt_next || !gt_intensity || !c ||
+	if ((event_channels != 1 && event_channels != 3 && event_channels != E3_EVENT_SHARED_FIRST_VIEW) || width <= 0 || height <= 0 || !image || !image_now || !image_next || !gt_now || !gt_next || !gt_intensity || !c ||
 		!scratch || scratch_bytes < 8 * sizeof(double) || (reinterpret_cast<size_t>(scratch) & 7) || !d_image || !d_image_now ||
 		!d_image_next || !out5)
 		return E3_ERR_BAD_ARGUMENT;
@@ -446,7 +467,11 @@ static cudaError_t view_streams(ViewStreams** out)
 int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 {
 	if (!a) return E3_ERR_BAD_ARGUMENT;
-	if (a->views[1].channels != a->views[2].channels || a->views[0].channels != 3) return E3_ERR_BAD_ARGUMENT;
+	// views[1].channels == 0: the first event view IS the intensity view (same camera) and is rendered once
+	const bool shared = a->views[1].channels == 0;
+	if (a->views[0].channels != 3) return E3_ERR_BAD_ARGUMENT;
+	if (shared ? (a->views[2].channels != 1 || !a->views[1].seed || !a->d_mean2D) : (a->views[1].channels != a->views[2].channels))
+		return E3_ERR_BAD_ARGUMENT;
 	cudaStream_t main_st = (cudaStream_t)stream;
 	ViewStreams* vs = nullptr;
 	E3_CHECK(view_streams(&vs));
@@ -455,6 +480,7 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
 	for (int k = 0; k < 3; k++) {
+		if (shared && k == 1) continue;
 		const e3_view& v = a->views[k];
 		int rc = e3_rasterize_forward_raw_ws(v.geometry_buffer, v.binning_buffer, (size_t)a->binning_capacity, v.image_buffer,
 			v.num_rendered_host, a->P, a->active_sh_degree, v.channels, a->background, a->width, a->height, a->xyz, a->features_dc,
@@ -469,9 +495,9 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	if (a->forwards_done_event) E3_CHECK(cudaEventRecord((cudaEvent_t)a->forwards_done_event, main_st));
 	if (a->P == 0) return 0;
 	if (a->wait_before_loss_event) E3_CHECK(cudaStreamWaitEvent(main_st, (cudaEvent_t)a->wait_before_loss_event, 0));
-	int rc = e3_event_loss(a->width, a->height, a->views[0].out_color, a->views[1].out_color, a->views[2].out_color, a->gt_now,
+	int rc = e3_event_loss(a->width, a->height, a->views[0].out_color, a->views[shared ? 0 : 1].out_color, a->views[2].out_color, a->gt_now,
 		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, a->loss_upstream != 0.f ? a->loss_upstream : 1.0f,
-		a->views[1].channels, a->loss_scratch, 64,
+		shared ? E3_EVENT_SHARED_FIRST_VIEW : a->views[1].channels, a->loss_scratch, 64,
 		a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, main_st);
 	if (rc) return rc;
 	// ---- per view, on its own stream: backward blend, then the gradient accumulation. The three
@@ -490,14 +516,19 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
 	for (int k = 0; k < 3; k++) {
+		if (shared && k == 1) continue;
 		const e3_view& v = a->views[k];
 		{
+			// shared first view: one backward blend with two seeds -- views[1].seed holds the total seed of the
+			// view (parameter gradients), views[0].seed the intensity term's (d_mean2D), see e3_rasterize_backward_raw_dual
+			const float* seed = (shared && k == 0) ? a->views[1].seed : v.seed;
+			const float* stats = (shared && k == 0) ? a->views[0].seed : nullptr;
 			rc = backward_raw_impl(3, a->P, a->active_sh_degree, v.channels, (int)a->binning_capacity, a->background, a->width,
 				a->height, a->xyz, a->features_dc, a->features_rest, a->opacity_logits, a->log_scales, a->scale_modifier,
 				a->raw_rotations, v.viewmatrix, v.projmatrix, v.cam_pos, v.tan_fovx, v.tan_fovy, v.radii, v.geometry_buffer,
-				v.binning_buffer, v.image_buffer, v.seed, 1, a->d_xyz, a->d_features_dc,
+				v.binning_buffer, v.image_buffer, seed, 1, a->d_xyz, a->d_features_dc,
 				a->d_features_rest, a->d_opacity_logits, a->d_log_scales, a->d_raw_rotations, k == 0 ? a->d_mean2D : nullptr, 0,
-				sts[k], a->grad_multicast_delta);
+				sts[k], a->grad_multicast_delta, stats);
 			if (rc) return rc;
 		}
 	}

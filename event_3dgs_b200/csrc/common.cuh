@@ -129,6 +129,9 @@ struct E3Frame {
 	// != 0: byte offset from a gradient pointer to its NVLS multicast alias; accumulating gradient
 	// writes then go out as multimem.red (reduced into every rank's copy by the NVSwitch)
 	long long mc_delta = 0;
+	// the screen-space gradient handed out (d_mean2D) comes from accumulator slots 9, 10 (the second seed
+	// of a dual backward blend) instead of slots 0, 1
+	bool mean2d_from_second_seed = false;
 };
 
 cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const float* scales,
@@ -169,7 +172,7 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, cons
 	uint32_t* n_contrib, float* out_color, cudaStream_t st);
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
-	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st);
+	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st, const float* dL_dpix2 = nullptr);
 
 // knn.cu
 int e3_knn_grid_dim(int P);

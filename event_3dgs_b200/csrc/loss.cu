@@ -58,7 +58,7 @@ __device__ __forceinline__ double block_sum(double v, double* sm)
 
 // sums[0] = sum |d - g|, [1] = #(g != 0), [2] = sum |image - gt_int| (3N terms),
 // [3] = sum |image - gt_blur|, [4] = sum sgn(d - g) * d
-template <int EC, typename GT>
+template <int ECN, int ECX, typename GT>
 __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const float* __restrict__ image,
 	const float* __restrict__ image_now, const float* __restrict__ image_next, const GT* __restrict__ gt_now,
 	const GT* __restrict__ gt_next, const GT* __restrict__ gt_int, const GT* __restrict__ gt_blur,
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 	const float c = __ldg(c_ptr);
 	double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0;
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
-		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
+		const float y1 = luma_ev<ECN>(image_now, i, N), y2 = luma_ev<ECX>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
 		const float g = (logf(luma_gt<GT>(gt_next, i, N) + EVT_EPS) - logf(luma_gt<GT>(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		s0 += fabsf(d - g);
@@ -91,7 +91,10 @@ __global__ void __launch_bounds__(256) event_loss_reduce_kernel(size_t N, const 
 
 // out[0] = loss, out[1] = dL/dc, out[2] = loss1 (event L1), out[3] = loss2 (intensity L1),
 // out[4] = fraction of pixels with a non-zero GT event difference
-template <int EC, typename GT>
+// TOT (shared first view: image_now IS image, rendered once): d_now receives the TOTAL seed of that view,
+// event-now term + intensity term, while d_image keeps the intensity term alone (the second seed of the
+// dual backward blend)
+template <int ECN, int ECX, bool TOT, typename GT>
 __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const float* __restrict__ image,
 	const float* __restrict__ image_now, const float* __restrict__ image_next, const GT* __restrict__ gt_now,
 	const GT* __restrict__ gt_next, const GT* __restrict__ gt_int, const GT* __restrict__ gt_blur,
@@ -114,40 +117,43 @@ __global__ void __launch_bounds__(256) event_loss_seed_kernel(size_t N, const fl
 		out[2] = (float)loss1; out[3] = (float)loss2; out[4] = (float)f;
 	}
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (size_t)gridDim.x * blockDim.x) {
-		const float y1 = luma_ev<EC>(image_now, i, N), y2 = luma_ev<EC>(image_next, i, N);
+		const float y1 = luma_ev<ECN>(image_now, i, N), y2 = luma_ev<ECX>(image_next, i, N);
 		const float d = (logf(y2 + EVT_EPS) - logf(y1 + EVT_EPS)) / c;
 		const float g = (logf(luma_gt<GT>(gt_next, i, N) + EVT_EPS) - logf(luma_gt<GT>(gt_now, i, N) + EVT_EPS)) / 0.17f;
 		const float s = sgn(d - g);
 		const float dy2 = k1 * s / (c * (y2 + EVT_EPS));
 		const float dy1 = -k1 * s / (c * (y1 + EVT_EPS));
-		if (EC == 1) { d_now[i] = dy1; d_next[i] = dy2; }
-		else {
-			d_now[i] = LUMA_R * dy1; d_now[N + i] = LUMA_G * dy1; d_now[2 * N + i] = LUMA_B * dy1;
-			d_next[i] = LUMA_R * dy2; d_next[N + i] = LUMA_G * dy2; d_next[2 * N + i] = LUMA_B * dy2;
-		}
+		if (ECX == 1) d_next[i] = dy2;
+		else { d_next[i] = LUMA_R * dy2; d_next[N + i] = LUMA_G * dy2; d_next[2 * N + i] = LUMA_B * dy2; }
+		float gi[3];
 #pragma unroll
 		for (int ch = 0; ch < 3; ch++) {
 			const float v = __ldg(image + ch * N + i);
 			float gr = k2 * sgn(v - gt_load<GT>(gt_int, ch * N + i));
 			if (gt_blur) gr += k3 * sgn(v - gt_load<GT>(gt_blur, ch * N + i));
 			d_image[ch * N + i] = gr;
+			gi[ch] = TOT ? gr : 0.f;
 		}
+		if (ECN == 1) d_now[i] = dy1;
+		else { d_now[i] = LUMA_R * dy1 + gi[0]; d_now[N + i] = LUMA_G * dy1 + gi[1]; d_now[2 * N + i] = LUMA_B * dy1 + gi[2]; }
 	}
 }
 
 }  // namespace
 
-template <int EC, typename GT>
+template <int ECN, int ECX, bool TOT, typename GT>
 static void launch_loss(int grid, size_t N, const float* image, const float* image_now, const float* image_next, const void* gt_now,
 	const void* gt_next, const void* gt_int, const void* gt_blur, const float* c_ptr, float upstream, double* sums, float* d_image,
 	float* d_now, float* d_next, float* out, cudaStream_t st)
 {
-	event_loss_reduce_kernel<EC, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
+	event_loss_reduce_kernel<ECN, ECX, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
 		(const GT*)gt_int, (const GT*)gt_blur, c_ptr, sums);
-	event_loss_seed_kernel<EC, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
+	event_loss_seed_kernel<ECN, ECX, TOT, GT><<<grid, 256, 0, st>>>(N, image, image_now, image_next, (const GT*)gt_now, (const GT*)gt_next,
 		(const GT*)gt_int, (const GT*)gt_blur, c_ptr, sums, upstream, d_image, d_now, d_next, out);
 }
 
+// event_channels: 1 (both event renders are luma), 3 (both RGB), or E3_EVENT_SHARED_FIRST_VIEW (image_now is the
+// 3-channel intensity render itself, image_next a luma render; d_now = total seed of the shared view)
 cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
 	const void* gt_now, const void* gt_next, const void* gt_int, const void* gt_blur, int gt_is_u8, const float* c_ptr,
 	float upstream, int event_channels, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st)
@@ -156,8 +162,9 @@ cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* imag
 	if (e != cudaSuccess) return e;
 	const int grid = (int)min((size_t)148 * 8, (N + 255) / 256);
 #define ARGS grid, N, image, image_now, image_next, gt_now, gt_next, gt_int, gt_blur, c_ptr, upstream, sums, d_image, d_now, d_next, out, st
-	if (event_channels == 1) { if (gt_is_u8) launch_loss<1, uint8_t>(ARGS); else launch_loss<1, float>(ARGS); }
-	else { if (gt_is_u8) launch_loss<3, uint8_t>(ARGS); else launch_loss<3, float>(ARGS); }
+	if (event_channels == 1) { if (gt_is_u8) launch_loss<1, 1, false, uint8_t>(ARGS); else launch_loss<1, 1, false, float>(ARGS); }
+	else if (event_channels == 3) { if (gt_is_u8) launch_loss<3, 3, false, uint8_t>(ARGS); else launch_loss<3, 3, false, float>(ARGS); }
+	else { if (gt_is_u8) launch_loss<3, 1, true, uint8_t>(ARGS); else launch_loss<3, 1, true, float>(ARGS); }
 #undef ARGS
 	g_e3_launches += 2;
 	return cudaGetLastError();

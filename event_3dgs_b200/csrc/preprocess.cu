@@ -477,7 +477,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	float tan_fovx, float tan_fovy, float* __restrict__ acc,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
-	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot, long long mc)
+	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot, long long mc, bool mean2d_second)
 {
 	constexpr int BT = E3_PB_THREADS;
 	extern __shared__ __align__(16) float smem[];
@@ -552,7 +552,8 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 			if (!ACC || vis) put<ACC>(dL_dopacity + idx, dlogit, mc);
 		}
 	}
-	s_cov[3 * t] = a0.x; s_cov[3 * t + 1] = a0.y; s_cov[3 * t + 2] = 0.f;      // d mean2D row
+	// d mean2D row handed to the caller (densification statistics): slots 0, 1, or the second seed's 9, 10
+	s_cov[3 * t] = mean2d_second ? a2.y : a0.x; s_cov[3 * t + 1] = mean2d_second ? a2.z : a0.y; s_cov[3 * t + 2] = 0.f;
 
 	float3 dmean = make_float3(0, 0, 0);
 	float dcov[6] = { 0, 0, 0, 0, 0, 0 };
@@ -775,7 +776,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	kern<<<grid, BT, sm, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
-	dL_dscale, dL_drot, (AC) ? f.mc_delta : 0ll); } while (0)
+	dL_dscale, dL_drot, (AC) ? f.mc_delta : 0ll, f.mean2d_from_second_seed); } while (0)
 	if (raw && f.C == 1) {
 		if (shrest) { if (accumulate) LAUNCH(1, true, true, true); else LAUNCH(1, true, false, true); }
 		else { if (accumulate) LAUNCH(1, true, true, false); else LAUNCH(1, true, false, false); }

@@ -217,11 +217,35 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], int lane)
 	v[0] += __shfl_xor_sync(E3_FULL, v[0], 1);
 }
 
-template <int C>
+// Same for 16 slots: on return lane L with (L & 1) == 0 holds the full sum of slot
+// ((L>>4)&1)*8 + ((L>>3)&1)*4 + ((L>>2)&1)*2 + ((L>>1)&1) in v[0]. 16 shuffles.
+__device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane)
+{
+#pragma unroll
+	for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+		const bool hi = lane & bit;
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			if (k < half) {
+				const float send = hi ? v[k] : v[k + half];
+				const float keep = hi ? v[k + half] : v[k];
+				v[k] = keep + __shfl_xor_sync(E3_FULL, send, bit);
+			}
+		}
+	}
+	v[0] += __shfl_xor_sync(E3_FULL, v[0], 1);
+}
+
+// DUAL (3 channels only): a second seed dL_dpixels2 rides along, of which only the screen-space
+// gradient is wanted (accumulator slots 9, 10). Used when the intensity view and the first event view of
+// an iteration are the same camera and are rendered once: dL_dpixels is then the SUM of the two loss
+// terms' seeds (all parameter gradients are linear in it), dL_dpixels2 the intensity term alone, whose
+// screen-space gradient is what the reference's densification statistics accumulate (train.py:145,319-320).
+template <int C, bool DUAL>
 __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
 	int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
 	const float4* __restrict__ rec, const float* __restrict__ final_Ts,
-	const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+	const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels2,
 	float* __restrict__ acc)
 {
 	__shared__ float4 sAB[kBatchB * 2];
@@ -263,12 +287,21 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 		accum_rec[c] = 0.f; last_color[c] = 0.f;
 		bg_dot_dpixel += __ldg(bg + c) * dL_dpixel[c];
 	}
+	float dL_dpixel2[C];
+	float bg_dot_dpixel2 = 0.f;
+#pragma unroll
+	for (int c = 0; c < C; c++) {
+		dL_dpixel2[c] = (DUAL && inside) ? dL_dpixels2[c * HW + pix_id] : 0.f;
+		bg_dot_dpixel2 += __ldg(bg + c) * dL_dpixel2[c];
+	}
 	float last_alpha = 0.f;
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask), aId = smem_addr(sId);
 	// after warp_reduce8 lane L with (L & 3) == 0 holds slot my_slot of the accumulator row
-	const int my_slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-	const float slot_scale = my_slot == 0 ? ddelx_dx : my_slot == 1 ? ddely_dy : my_slot < 5 ? -0.5f : 1.0f;
+	const int my_slot = DUAL ? ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1)
+		: ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+	const float slot_scale = (my_slot == 0 || my_slot == 9) ? ddelx_dx : (my_slot == 1 || my_slot == 10) ? ddely_dy
+		: (my_slot >= 2 && my_slot < 5) ? -0.5f : 1.0f;
 
 	// instance index within the tile's list, walked from total-1 down to 0; an instance with
 	// 0-based index i has contributor number i (reference: `contributor--` before the test,
@@ -329,17 +362,19 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const float dchannel_dcolor = alpha * T;
 			float col[3];
 			col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? lds_f(aC + 4 * j) : 0.f;
-			float dL_dalpha = 0.0f;
+			float dL_dalpha = 0.0f, dL_dalpha2 = 0.0f;
 #pragma unroll
 			for (int c = 0; c < C; c++) {
 				const float ar = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
 				accum_rec[c] = valid ? ar : accum_rec[c];
 				last_color[c] = valid ? col[c] : last_color[c];
 				dL_dalpha += (col[c] - ar) * dL_dpixel[c];
+				if (DUAL) dL_dalpha2 += (col[c] - ar) * dL_dpixel2[c];
 			}
 			dL_dalpha *= T;
 			last_alpha = valid ? alpha : last_alpha;
 			dL_dalpha += (-T_final * ra) * bg_dot_dpixel;
+			if (DUAL) dL_dalpha2 = dL_dalpha2 * T + (-T_final * ra) * bg_dot_dpixel2;
 			const float dL_dG = b.y * dL_dalpha;
 			const float gdx = G * dx, gdy = G * dy;
 			const float dG_ddelx = -gdx * a.z - gdy * a.w;
@@ -355,6 +390,18 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			v[6] = dchannel_dcolor * dL_dpixel[0];
 			v[7] = 0.f;
 			if (C == 3) { v[7] = dchannel_dcolor * dL_dpixel[1]; v8 = dchannel_dcolor * dL_dpixel[2]; }
+			if (DUAL) {
+				const float dL_dG2 = b.y * dL_dalpha2;
+				float u[16];
+#pragma unroll
+				for (int i = 0; i < 8; i++) u[i] = v[i];
+				u[8] = v8; u[9] = dL_dG2 * dG_ddelx; u[10] = dL_dG2 * dG_ddely;
+				u[11] = u[12] = u[13] = u[14] = u[15] = 0.f;
+				warp_reduce16(u, lane);
+				if ((lane & 1) == 0 && my_slot < 11)
+					atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + my_slot, u[0] * slot_scale);
+				continue;
+			}
 			warp_reduce8(v, lane);
 			if (C == 3) {
 #pragma unroll
@@ -424,11 +471,13 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, cons
 
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order, const uint32_t* point_list,
 	const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
-	float* acc, cudaStream_t st)
+	float* acc, cudaStream_t st, const float* dL_dpix2)
 {
 	const unsigned grid = (unsigned)(f.gx * f.gy);
-	if (f.C == 1) render_bwd_kernel<1><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
-	else render_bwd_kernel<3><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, acc);
+	if (dL_dpix2 && f.C != 3) return cudaErrorInvalidValue;
+	if (dL_dpix2) render_bwd_kernel<3, true><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, dL_dpix2, acc);
+	else if (f.C == 1) render_bwd_kernel<1, false><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, nullptr, acc);
+	else render_bwd_kernel<3, false><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, nullptr, acc);
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }

@@ -152,7 +152,8 @@ def _forward_raw_ws(pc, cam, bg, scaling_modifier, debug, channels, ws, slot):
     return st
 
 
-def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling_modifier=1.0, debug=False):
+def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling_modifier=1.0, debug=False, stats_seed=None):
+    """stats_seed: second seed whose screen-space gradient alone is written to d_mean2D (e3_rasterize_backward_raw_dual)."""
     L = _lib.lib()
     xyz = pc._xyz
     P = xyz.shape[0]
@@ -161,13 +162,15 @@ def _backward_raw(pc, st, bg, dL_dpix, grads, accumulate, d_mean2D=None, scaling
     dev = xyz.device
     cam = st.cam
     D = int(pc.active_sh_degree)
+    fn = L.e3_rasterize_backward_raw if stats_seed is None else L.e3_rasterize_backward_raw_dual
+    seeds = (dL_dpix.data_ptr(),) if stats_seed is None else (dL_dpix.data_ptr(), stats_seed.data_ptr())
     with torch.cuda.device(dev):
-        code = L.e3_rasterize_backward_raw(
+        code = fn(
             P, D, st.channels, st.R, bg.data_ptr(), int(cam.image_width), int(cam.image_height), xyz.data_ptr(),
             pc._features_dc.data_ptr(), pc._features_rest.data_ptr(), pc._opacity.data_ptr(), pc._scaling.data_ptr(),
             float(scaling_modifier), pc._rotation.data_ptr(), cam.world_view_transform.data_ptr(),
             cam.full_proj_transform.data_ptr(), cam.camera_center.data_ptr(), st.tanfovx, st.tanfovy, st.radii.data_ptr(),
-            st.geom.data_ptr(), st.binning.data_ptr() if st.R > 0 else None, st.img.data_ptr(), dL_dpix.data_ptr(),
+            st.geom.data_ptr(), st.binning.data_ptr() if st.R > 0 else None, st.img.data_ptr(), *seeds,
             int(bool(accumulate)), grads["xyz"].data_ptr(), grads["features_dc"].data_ptr(),
             grads["features_rest"].data_ptr() if D > 0 else None, grads["opacity"].data_ptr(), grads["scaling"].data_ptr(),
             grads["rotation"].data_ptr(), None if d_mean2D is None else d_mean2D.data_ptr(), int(debug),
@@ -232,10 +235,12 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
 
     dedupe_views (opt-in): when the intensity camera and the first event camera are the same view
-    (see same_view) it is rendered ONCE and its two loss seeds are summed before one backward pass;
-    loss and parameter gradients are unchanged up to fp32 summation order. The screen-space
-    gradient handed to the densification statistics then contains both loss terms of that view
-    (the reference's contains only the intensity term), which is why this is not the default.
+    (see same_view; they are in the reference's datasets) it is rendered ONCE. Its backward blend carries
+    two seeds (e3_rasterize_backward_raw_dual): the sum of the intensity and the event term for the
+    parameter gradients, the intensity term alone for the screen-space gradient handed to the
+    densification statistics -- so loss, parameter gradients and statistics all equal the three-render
+    iteration up to fp32 summation order. Off by default only because the headline metric counts three
+    renders per view pair.
 
     gray_event_views: render the two event views with one channel, the luma that
     differentialable_event_simu takes of them anyway (utils/loss_utils.py:24-28,240-241); the
@@ -254,13 +259,17 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     ranks and scales the rest)."""
     if accumulate and getattr(pc, "_grad_flat", None) is None:
         raise RuntimeError("accumulate=True needs the gradients of a previous call")
-    if dedupe_views and same_view(cam_train, cam_now):
-        if accumulate:
-            raise RuntimeError("accumulate=True is not combined with dedupe_views")
-        return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg, gt_ready)
     for t in (pc._xyz, pc._features_dc, pc._features_rest, pc._scaling, pc._rotation, pc._opacity, c, bg):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("event_3dgs_b200.fused: tensors must be contiguous float32 CUDA tensors")
+    if dedupe_views and same_view(cam_train, cam_now):
+        ws = _workspace_for(pc, cam_train) if no_sync and pc._xyz.shape[0] > 0 else None
+        if ws is not None:
+            return _event_iteration_single_call(pc, (cam_train, cam_now, cam_next), gt, c, bg, deblur, return_pkg, 1, gt_ready,
+                                                accumulate, ws, shared=True)
+        if accumulate:
+            raise RuntimeError("accumulate=True with dedupe_views needs the workspace of a previous call")
+        return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg, gt_ready, no_sync)
     ec = 1 if gray_event_views else 3
     ws = _workspace_for(pc, cam_train) if no_sync and pc._xyz.shape[0] > 0 else None
     if ws is not None:
@@ -310,7 +319,7 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     return loss
 
 
-def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, gt_ready, accumulate, ws):
+def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, gt_ready, accumulate, ws, shared=False):
     """The whole iteration through ONE C call (e3_event_iteration) on the persistent workspace: no host
     synchronisation, no per-render Python work. Falls back to itself once if the workspace overflowed."""
     L = _lib.lib()
@@ -335,11 +344,15 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
         grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D, flat=ex.buf)
     else:
         grads = pc._grad_views if accumulate else _alloc_grads(pc, c, D)
-    chans = (3, ec, ec)
-    colors = [torch.empty(ch, H, W, dtype=torch.float32, device=dev) for ch in chans]
-    radii = [torch.empty(P, dtype=torch.int32, device=dev) for _ in range(3)]
+    # shared: the first event view is the intensity view (same camera): it is rendered once (channels 0 =
+    # "not rendered"), the next view as luma; the backward blend of the shared view carries two seeds
+    chans = (3, 0, 1) if shared else (3, ec, ec)
+    colors = [torch.empty(ch, H, W, dtype=torch.float32, device=dev) if ch else None for ch in chans]
+    radii = [torch.empty(P, dtype=torch.int32, device=dev) if ch else None for ch in chans]
     out = torch.empty(5, dtype=torch.float32, device=dev)
-    d_mean2D = None if accumulate else torch.empty_like(pc._xyz)
+    d_mean2D = None if (accumulate and not shared) else torch.empty_like(pc._xyz)
+    if shared:
+        ws.r_host[1].zero_()
     a = ws.args
     a.P, a.active_sh_degree, a.width, a.height = P, D, W, H
     a.binning_capacity, a.scale_modifier, a.accumulate = ws.cap, 1.0, int(bool(accumulate) or mc is not None)
@@ -357,7 +370,10 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
         v.viewmatrix, v.projmatrix, v.cam_pos = cam.world_view_transform.data_ptr(), cam.full_proj_transform.data_ptr(), cam.camera_center.data_ptr()
         v.tan_fovx, v.tan_fovy, v.channels = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), chans[k]
         v.geometry_buffer, v.binning_buffer, v.image_buffer = ws.geom[k].data_ptr(), ws.bin[k].data_ptr(), ws.img[k].data_ptr()
-        v.out_color, v.radii, v.seed = colors[k].data_ptr(), radii[k].data_ptr(), ws.seed(k, chans[k]).data_ptr()
+        if chans[k]:
+            v.out_color, v.radii, v.seed = colors[k].data_ptr(), radii[k].data_ptr(), ws.seed(k, chans[k]).data_ptr()
+        else:       # only the seed buffer of the skipped view is used: the total seed of the shared view
+            v.out_color, v.radii, v.seed = None, None, ws.seed(k, 3).data_ptr()
         v.num_rendered_host = ws.r_host[k].data_ptr()
     a.gt_now, a.gt_next, a.gt_intensity = gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr()
     a.gt_blur = None if blur is None else blur.data_ptr()
@@ -377,7 +393,9 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
                                "into the other ranks; enlarge the workspace (Workspace.resize) and repeat the optimizer step")
         if accumulate:
             raise RuntimeError("event_3dgs_b200.fused: workspace overflow during an accumulating step; repeat the optimizer step")
-        return _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, None, accumulate, ws)
+        return _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, None, accumulate, ws, shared)
+    if shared:
+        Rs = [Rs[0], Rs[2]]
     if mc is not None:
         # dL/dc comes from the loss kernel (already scaled by loss_upstream): reduce it into every rank's copy too
         with torch.cuda.device(dev):
@@ -417,17 +435,21 @@ def _remember_workspace(pc, cam, r_max):
     pc._e3_ws = Workspace(pc._xyz.shape[0], int(cam.image_width), int(cam.image_height), pc._xyz.device, int(r_max * 1.3) + 4096)
 
 
-def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg, gt_ready=None):
+def _event_iteration_two_renders(pc, cam_a, cam_next, gt, c, bg, deblur, return_pkg, gt_ready=None, no_sync=True):
     st_a = _forward_raw(pc, cam_a, bg)
     st_n = _forward_raw(pc, cam_next, bg)
+    if no_sync and pc._xyz.shape[0] > 0:
+        _remember_workspace(pc, cam_a, max(st_a.R, st_n.R))
     if gt_ready is not None:
         torch.cuda.current_stream(pc._xyz.device).wait_event(gt_ready)
     out, seeds = event_loss_and_seeds(st_a.color, st_a.color, st_n.color, gt, c, deblur)
-    seeds["image"].add_(seeds["image_now"])
+    # one backward blend of the shared view with both seeds: parameter gradients from their sum, the
+    # screen-space gradient (densification statistics) from the intensity term alone, as in the reference
+    total = seeds["image_now"].add_(seeds["image"])
     D = int(pc.active_sh_degree)
     grads = _alloc_grads(pc, c, D)
     d_mean2D = torch.empty_like(pc._xyz)
-    _backward_raw(pc, st_a, bg, seeds["image"], grads, False, d_mean2D)
+    _backward_raw(pc, st_a, bg, total, grads, False, d_mean2D, stats_seed=seeds["image"])
     _backward_raw(pc, st_n, bg, seeds["image_next"], grads, True)
     pc._xyz.grad = grads["xyz"]
     pc._features_dc.grad = grads["features_dc"]

@@ -80,7 +80,7 @@ class Trainer:
     otherwise one [3,H,W] frame."""
 
     def __init__(self, pc, cams_train, cams_event, gt_for, opt=None, event=True, gray=True, deblur=False, extent=1.0,
-                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True, dedupe_views=False):
+                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True, dedupe_views=True):
         self.pc, self.cams_train, self.cams_event, self.gt_for = pc, cams_train, cams_event, gt_for
         self.opt = opt or optimization_defaults()
         self.event, self.gray, self.deblur = event, gray, deblur
@@ -88,13 +88,10 @@ class Trainer:
         self.white_background = white_background
         self.rank, self.world = rank, world
         self.fused_exchange = fused_exchange
-        # opt-in (fused.event_iteration_backward): render the intensity view and the first event view once when
-        # they are the same camera (they are, in the reference's datasets); the densification statistics then
-        # see both loss terms of that view, which is why it is not the default
+        # render the intensity view and the first event view once whenever they are the same camera (they are,
+        # in the reference's datasets): loss, gradients and densification statistics are those of the
+        # three-render iteration (fused.event_iteration_backward, dedupe_views); False forces three renders
         self.dedupe_views = dedupe_views
-        if dedupe_views and pairs_per_step != world:
-            raise ValueError("dedupe_views needs one view pair per rank and step")
-        self.last_exchange = "none"
         if pairs_per_step % world:
             raise ValueError("pairs_per_step must be a multiple of the number of ranks")
         self.pairs_per_step = pairs_per_step

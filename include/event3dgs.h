@@ -210,6 +210,27 @@ E3_API int e3_rasterize_backward_raw(
 	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
 	int debug, void* stream);
 
+/* e3_rasterize_backward_raw with TWO seeds for one 3-channel render: all parameter gradients come from
+ * dL_dpix, d_mean2D (required) comes from dL_dpix_stats alone. For an event iteration whose intensity
+ * camera and first event camera are the same view (they are in the reference's datasets,
+ * scene/dataset_readers.py:145-160): the reference renders that view twice (train.py:144,159-160);
+ * rendered once, dL_dpix = seed of the intensity term + seed of the event term gives the same parameter
+ * gradients (they are linear in the seed), and dL_dpix_stats = the intensity term's seed gives the
+ * screen-space gradient that the reference's densification statistics take from its FIRST render
+ * (train.py:145,319-320) -- so nothing observable changes. */
+E3_API int e3_rasterize_backward_raw_dual(
+	int P, int active_sh_degree, int channels, int R,
+	const float* background, int width, int height,
+	const float* xyz, const float* features_dc, const float* features_rest, const float* opacity_logits,
+	const float* log_scales, float scale_modifier, const float* raw_rotations,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, const int* radii,
+	char* geometry_buffer, char* binning_buffer, char* image_buffer,
+	const float* dL_dpix, const float* dL_dpix_stats, int accumulate,
+	float* d_xyz, float* d_features_dc, float* d_features_rest, float* d_opacity_logits,
+	float* d_log_scales, float* d_raw_rotations, float* d_mean2D,
+	int debug, void* stream);
+
 /* Event loss of train.py:165-203 (with utils/loss_utils.py:24-28, 234-249, 270-271), value and
  * backward seeds in two streaming kernels. Inputs are [3,H,W] float images: the three renders
  * (image = intensity view, image_now / image_next = event views index / index+1), the GT event
@@ -222,6 +243,11 @@ E3_API int e3_rasterize_backward_raw(
  * (channels = 1 of e3_rasterize_forward_raw) and the seeds are [1,H,W]. scratch: >= 64 bytes,
  * 8-byte aligned device memory. Outputs: the three seeds dL/dimage* [3,H,W] and
  * out5 = { loss, dL/dc, event L1, intensity L1, fraction of pixels with non-zero GT event }. */
+/* event_channels value for a render triplet whose first event view IS the intensity view (rendered once):
+ * image_now must be the 3-channel `image` itself, image_next a 1-channel luma render; d_image_now then
+ * receives the TOTAL seed of the shared view (event term + intensity term) and d_image the intensity
+ * term alone -- the two seeds of e3_rasterize_backward_raw_dual. */
+#define E3_EVENT_SHARED_FIRST_VIEW 0x31
 E3_API int e3_event_loss(int width, int height, const float* image, const float* image_now,
 	const float* image_next, const void* gt_now, const void* gt_next, const void* gt_intensity,
 	const void* gt_blur, int gt_is_u8, const float* c, float upstream, int event_channels, void* scratch,
@@ -343,7 +369,10 @@ E3_API int e3_l1_ssim_loss(int width, int height, int gray, const float* image, 
  * (channels 1 = luma, or 3). seed buffers are [channels,H,W]. d_* receive the SUM of the three
  * backward passes (zeroed first, or added to when accumulate != 0; the three views run on three
  * streams and add with vector reductions, so the summation order, like that of the blend's atomics,
- * is not fixed from run to run); d_mean2D (optional) is the screen-space gradient of views[0]. out5 as in e3_event_loss. After the stream has passed the
+ * is not fixed from run to run); d_mean2D (optional) is the screen-space gradient of views[0]. out5 as in e3_event_loss.
+ * views[1].channels == 0 selects the shared-first-view form (E3_EVENT_SHARED_FIRST_VIEW): views[1] is not
+ * rendered, only its seed buffer ([3,H,W]) is used, views[2].channels must be 1 and d_mean2D is required.
+ * After the stream has passed the
  * read-backs, check views[k].num_rendered_host[0] <= binning_capacity (see
  * e3_rasterize_forward_raw_ws). */
 typedef struct e3_view {

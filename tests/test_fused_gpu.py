@@ -142,13 +142,29 @@ def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev):
     pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, 0, True)
     leaves = pc.leaves() + [c]
     assert fused.same_view(cams[3], cams[3]) and not fused.same_view(cams[3], cams[4])
-    la = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True)
+    la, pa = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, return_pkg=True,
+                                            gray_event_views=False)
     ga = [p.grad.clone() for p in leaves]
-    lb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
-    gb = [p.grad.clone() for p in leaves]
-    assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
-    for a, b in zip(ga, gb):
-        assert rel_err(b.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    # both routes of the two-render iteration: separate calls (no_sync=False) and the single C call on the workspace
+    for no_sync in (False, True):
+        lb, pb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True,
+                                                return_pkg=True, no_sync=no_sync)
+        gb = [p.grad.clone() for p in leaves]
+        assert len(pb["num_rendered"]) == 2
+        assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item()), no_sync
+        for a, b in zip(ga, gb):
+            assert rel_err(b.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4, no_sync
+        # the screen-space gradient of the first render (densification statistics, train.py:319-320) is the
+        # intensity term's alone in both: the shared view's backward blend carries it as a second seed
+        va, vb = pa["viewspace_points"].grad, pb["viewspace_points"].grad
+        assert rel_err(vb.cpu().numpy(), va.cpu().numpy()) < 1e-4, no_sync
+        assert float(vb[:, 2].abs().max()) == 0.0 and torch.equal(pa["radii"], pb["radii"])
+        assert torch.equal(pa["render"].view(torch.int32), pb["render"].view(torch.int32))
+    # accumulation over view pairs works on the shared route too
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True, accumulate=True)
+    for a, p in zip(ga, leaves):
+        assert rel_err(p.grad.cpu().numpy(), 2.0 * a.cpu().numpy(), 1e-20) < 2e-3
     # different views: the flag changes nothing
     lc = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True, dedupe_views=True)
     ld = fused.event_iteration_backward(pc, cams[2], cams[3], cams[4], gt, c, bg, deblur=True)
