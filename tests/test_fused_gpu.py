@@ -137,9 +137,11 @@ def test_dist2_matches_bruteforce_oracle(cuda_dev):
     assert np.allclose(got[idx], ref, rtol=1e-4)
 
 
-def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev):
+@pytest.mark.parametrize("sh_degree", [0, 2])
+def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev, sh_degree):
     from event_3dgs_b200 import fused
-    pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, 0, True)
+    pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, sh_degree, True)
+    bg = torch.tensor([0.3, 0.1, 0.6], device=cuda_dev)          # a coloured background goes through both seeds too
     leaves = pc.leaves() + [c]
     assert fused.same_view(cams[3], cams[3]) and not fused.same_view(cams[3], cams[4])
     la, pa = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, deblur=True, return_pkg=True,
