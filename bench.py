@@ -534,7 +534,14 @@ def main():
             trn.step()
         ms_t, _, _ = timed(lambda s: trn.step(), args.steps)
         line["train_loop"] = {"value": 1e3 / (ms_t / args.steps), "unit": UNIT, "ms_per_step": ms_t / args.steps,
-                              "what": "iteration + densification statistics + fused Adam (6 groups) + Adam(c), one view-pair per step"}
+                              "what": "iteration + densification statistics + fused Adam (6 groups) + Adam(c), one view-pair per step; Trainer default: the intensity view and the first event view (same camera) are rendered once, results as with three renders"}
+        trn3 = tr.Trainer(pl.GaussianParams(scene["gaussians"], dev), cams, cams, lambda i: gt_dev, opt=tr.optimization_defaults(densify_from_iter=10 ** 9),
+                          event=True, deblur=deblur, extent=2.6, dedupe_views=False)
+        for s in range(3):
+            trn3.step()
+        ms_t3, _, _ = timed(lambda s: trn3.step(), args.steps)
+        line["train_loop"]["three_renders"] = {"value": 1e3 / (ms_t3 / args.steps), "unit": UNIT, "ms_per_step": ms_t3 / args.steps}
+        del trn3
         del trn, pc_t
 
     if use_fused and world == 1:
