@@ -99,7 +99,7 @@ def snapshot(gm, prefix):
     return out
 
 
-def case(seed, P, extent, max_screen_size, iters):
+def case(seed, P, extent, max_screen_size, iters, poke_inf=0):
     DRAWS.clear()
     gm, g = build_model(seed, P, extent)
     out = snapshot(gm, "in_")
@@ -115,6 +115,11 @@ def case(seed, P, extent, max_screen_size, iters):
         grad_all.append(vsp.grad.numpy())
     out["radii"] = np.stack(radii_all)
     out["viewspace_grad"] = np.stack(grad_all)
+    if poke_inf:
+        # rows whose gradient norm was accumulated but whose visit count is zero: accum / denom = inf, which the
+        # reference neither masks nor clamps (only NaN is zeroed, gaussian_model.py:391) -> they are selected
+        seen = torch.nonzero(gm.xyz_gradient_accum[:, 0] > 0)[:poke_inf, 0]
+        gm.denom[seen] = 0
     out.update({k.replace("in_", "stats_"): v for k, v in snapshot(gm, "in_").items() if k in ("in_accum", "in_denom", "in_max_radii2D")})
     gm.densify_and_prune(0.0002, 0.005, extent, max_screen_size)
     out.update(snapshot(gm, "out_"))
@@ -125,12 +130,14 @@ def case(seed, P, extent, max_screen_size, iters):
     out["reset_m"] = gm.optimizer.state[p]["exp_avg"].numpy().copy()
     out["extent"] = np.float32(extent)
     out["max_screen_size"] = np.int32(max_screen_size or 0)
+    out["poke_inf"] = np.int32(poke_inf)
     return out
 
 
 if __name__ == "__main__":
     for name, kw in (("densify_a", dict(seed=1, P=300, extent=4.0, max_screen_size=None, iters=3)),
-                     ("densify_b", dict(seed=2, P=400, extent=2.5, max_screen_size=20, iters=2))):
+                     ("densify_b", dict(seed=2, P=400, extent=2.5, max_screen_size=20, iters=2)),
+                     ("densify_c", dict(seed=3, P=200, extent=3.0, max_screen_size=20, iters=1, poke_inf=25))):
         d = case(**kw)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **d)
         print(name, "P", kw["P"], "->", d["out_xyz"].shape[0], "rows; split draws", d["z"].shape[0])
