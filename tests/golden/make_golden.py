@@ -111,6 +111,27 @@ def schedule_golden():
                "views_event": ev, "views_frame": fr}, open(os.path.join(HERE, "schedule.json"), "w"), indent=1)
 
 
+def cameras_golden():
+    """tests/golden/cameras.npz: the camera tensors of scene/cameras.py:48-57, computed with the reference's own
+    utils/graphics_utils.py (getWorld2View2, getProjectionMatrix) for the (R, T, FoV) of a few synthetic views."""
+    from utils.graphics_utils import getProjectionMatrix, getWorld2View2
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from event_3dgs_b200 import synthetic as syn
+    out = {}
+    for n, (i, W, H) in enumerate(((0, 64, 64), (7, 346, 260), (50, 1280, 720))):
+        cam = syn.make_camera(i, 96, W, H)
+        R, T = cam["R"], cam["T"]
+        wvt = torch.tensor(getWorld2View2(R, T, np.array([0.0, 0.0, 0.0]), 1.0)).transpose(0, 1)
+        proj = getProjectionMatrix(znear=0.01, zfar=100.0, fovX=cam["FoVx"], fovY=cam["FoVy"]).transpose(0, 1)
+        full = (wvt.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0)
+        center = wvt.inverse()[3, :3]
+        out["view%d_index" % n] = np.array([i, W, H])
+        out["view%d_world_view_transform" % n] = wvt.numpy()
+        out["view%d_full_proj_transform" % n] = full.numpy()
+        out["view%d_camera_center" % n] = center.numpy()
+    np.savez_compressed(os.path.join(HERE, "cameras.npz"), **out)
+
+
 if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "event_loss_a.npz"), **event_case(0, 24, 40, False, 0.7))
     np.savez_compressed(os.path.join(HERE, "event_loss_b.npz"), **event_case(1, 17, 33, True, 0.3))
@@ -119,5 +140,6 @@ if __name__ == "__main__":
     np.savez_compressed(os.path.join(HERE, "l1_ssim_gray.npz"), **ssim_case(4, 37, 50, True))
     np.savez_compressed(os.path.join(HERE, "l1_ssim_rgb.npz"), **ssim_case(5, 33, 20, False))
     schedule_golden()
+    cameras_golden()
     print("golden vectors written to", HERE)
 

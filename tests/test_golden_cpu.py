@@ -123,3 +123,21 @@ def test_c_oracle_against_reference_cuda_golden(name, cs):
         assert rel_err(g[k].reshape(d[k].shape), d[k], fl if k == "dL_drotations" else 0.0) < 1e-4, k
     conic = d["dL_dconic"].reshape(P, 4)
     assert rel_err(g["dL_dconic"], conic) < 1e-4
+
+
+def test_synthetic_cameras_follow_the_reference_camera_recipe():
+    """event_3dgs_b200.synthetic.make_camera against scene/cameras.py:48-57 evaluated with the reference's own
+    utils/graphics_utils.py (tests/golden/cameras.npz): transposed storage, full_proj = view . proj,
+    camera_center = inverse(view)[3, :3]."""
+    from event_3dgs_b200 import synthetic as syn
+    d = np.load(os.path.join(G, "cameras.npz"))
+    n = 0
+    while "view%d_index" % n in d:
+        i, W, H = (int(x) for x in d["view%d_index" % n])
+        cam = syn.make_camera(i, 96, W, H)
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            want = d["view%d_%s" % (n, k)]
+            assert cam[k].shape == want.shape and cam[k].dtype == np.float32
+            assert np.abs(cam[k] - want).max() <= 2e-6 * max(1.0, np.abs(want).max()), (n, k)
+        n += 1
+    assert n == 3
