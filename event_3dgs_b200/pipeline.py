@@ -86,6 +86,27 @@ class GaussianParams(nn.Module):
         return [self._xyz, self._features_dc, self._features_rest, self._scaling, self._rotation, self._opacity]
 
 
+def create_from_pcd(points, colors, device, sh_degree=3):
+    """GaussianModel.create_from_pcd (scene/gaussian_model.py:124-147), the call site of distCUDA2: xyz = the
+    points, SH DC = RGB2SH(colours) (utils/sh_utils.py:114-115), the rest 0, isotropic log-scale =
+    log(sqrt(clamp_min(distCUDA2(points), 1e-7))), rotation (1,0,0,0), opacity = inverse_sigmoid(0.1).
+    points / colors: [P,3] arrays or tensors, colours in [0,1]. Returns GaussianParams at SH degree 0."""
+    from .knn import distCUDA2
+    pts = torch.as_tensor(points, dtype=torch.float32).to(device).contiguous()
+    col = torch.as_tensor(colors, dtype=torch.float32).to(device)
+    P = pts.shape[0]
+    dist2 = torch.clamp_min(distCUDA2(pts), 0.0000001)
+    scales = torch.log(torch.sqrt(dist2))[..., None].repeat(1, 3)
+    rots = torch.zeros(P, 4, device=device)
+    rots[:, 0] = 1
+    x = 0.1 * torch.ones(P, 1, dtype=torch.float32, device=device)
+    g = {"xyz": pts, "features_dc": ((col - 0.5) / C0).view(P, 1, 3), "features_rest": torch.zeros(P, (sh_degree + 1) ** 2 - 1, 3, device=device),
+         "scaling": scales, "rotation": rots, "opacity": torch.log(x / (1 - x)), "active_sh_degree": 0}
+    pc = GaussianParams(g, device)
+    pc.max_sh_degree = sh_degree
+    return pc
+
+
 def make_camera(cam, device, image=None):
     """numpy camera dict of synthetic.make_camera -> the attributes render() reads (scene/cameras.py)."""
     t = lambda a: torch.as_tensor(a, dtype=torch.float32).to(device)

@@ -134,6 +134,42 @@ def case(seed, P, extent, max_screen_size, iters, poke_inf=0):
     return out
 
 
+def init_case(seed, P):
+    """GaussianModel.create_from_pcd (scene/gaussian_model.py:124-147) run by the reference itself. Its
+    distCUDA2 (simple-knn, not in the tree) is replaced by an exact brute-force 3-NN in float64 -- the contract
+    of that function --, Tensor.cuda by the identity."""
+    import scene.gaussian_model as gmod
+    from utils.graphics_utils import BasicPointCloud
+
+    def dist2_bruteforce(pts):
+        p = pts.double()
+        d = torch.cdist(p, p) ** 2
+        d.fill_diagonal_(float("inf"))
+        return d.topk(3, largest=False).values.mean(1).float()
+    gmod.distCUDA2 = dist2_bruteforce
+    cuda, ones = torch.Tensor.cuda, torch.ones
+    torch.Tensor.cuda = lambda self, *a, **k: self
+
+    def ones_on_cpu(*a, **k):
+        k.pop("device", None)
+        return ones(*a, **k)
+    torch.ones = ones_on_cpu
+    try:
+        g = torch.Generator().manual_seed(seed)
+        pts = (torch.rand(P, 3, generator=g) * 2.6 - 1.3).numpy()
+        cols = torch.rand(P, 3, generator=g).numpy()
+        gm = GaussianModel(3)
+        import io
+        import contextlib
+        with contextlib.redirect_stdout(io.StringIO()):
+            gm.create_from_pcd(BasicPointCloud(points=pts, colors=cols, normals=np.zeros_like(pts)), 1.0)
+    finally:
+        torch.Tensor.cuda, torch.ones = cuda, ones
+    return dict(points=pts, colors=cols, xyz=gm._xyz.detach().numpy(), features_dc=gm._features_dc.detach().numpy(),
+                features_rest=gm._features_rest.detach().numpy(), scaling=gm._scaling.detach().numpy(),
+                rotation=gm._rotation.detach().numpy(), opacity=gm._opacity.detach().numpy())
+
+
 if __name__ == "__main__":
     for name, kw in (("densify_a", dict(seed=1, P=300, extent=4.0, max_screen_size=None, iters=3)),
                      ("densify_b", dict(seed=2, P=400, extent=2.5, max_screen_size=20, iters=2)),
@@ -141,3 +177,5 @@ if __name__ == "__main__":
         d = case(**kw)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **d)
         print(name, "P", kw["P"], "->", d["out_xyz"].shape[0], "rows; split draws", d["z"].shape[0])
+    np.savez_compressed(os.path.join(HERE, "init_pcd.npz"), **init_case(7, 1500))
+    print("init_pcd written")

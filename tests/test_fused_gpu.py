@@ -381,3 +381,18 @@ def test_tight_instance_lists_do_not_change_the_image(cuda_dev):
             assert 0 < st.R < 0.95 * R_ref, (st.R, R_ref)
             d = float((st.color - ref["render"]).abs().max())
             assert d < 3e-6, d
+
+
+def test_create_from_pcd_matches_reference_initialisation(cuda_dev):
+    """pipeline.create_from_pcd (e3_dist2 inside) against the reference's GaussianModel.create_from_pcd run on the
+    same point cloud (tests/golden/init_pcd.npz)."""
+    import os
+    from event_3dgs_b200 import pipeline as pl
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "init_pcd.npz"))
+    pc = pl.create_from_pcd(d["points"], d["colors"], cuda_dev)
+    for name, attr, tol in (("xyz", "_xyz", 0.0), ("features_dc", "_features_dc", 1e-6), ("features_rest", "_features_rest", 0.0),
+                            ("scaling", "_scaling", 2e-6), ("rotation", "_rotation", 0.0), ("opacity", "_opacity", 1e-6)):
+        got = getattr(pc, attr).detach().cpu().numpy()
+        assert got.shape == d[name].shape, name
+        assert np.abs(got - d[name]).max() <= tol, name
+    assert pc.active_sh_degree == 0 and pc.max_sh_degree == 3

@@ -141,3 +141,14 @@ def test_synthetic_cameras_follow_the_reference_camera_recipe():
             assert np.abs(cam[k] - want).max() <= 2e-6 * max(1.0, np.abs(want).max()), (n, k)
         n += 1
     assert n == 3
+
+
+def test_knn_oracle_reproduces_reference_initial_scales():
+    """oracle dist2 (brute-force 3-NN in C) against the log-scales the reference's create_from_pcd computed
+    (tests/golden/init_pcd.npz, made by running scene/gaussian_model.py:124-147 with an exact float64 3-NN)."""
+    from oracle import raster_oracle as ro
+    d = np.load(os.path.join(G, "init_pcd.npz"))
+    d2 = np.maximum(ro.dist2(d["points"].astype(np.float32)), 1e-7)
+    got = np.log(np.sqrt(d2))
+    assert np.abs(got[:, None] - d["scaling"]).max() < 2e-6
+    assert np.allclose(d["rotation"], np.array([[1.0, 0, 0, 0]])) and np.allclose(d["opacity"], np.log(0.1 / 0.9), atol=1e-6)
