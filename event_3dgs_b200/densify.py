@@ -10,7 +10,6 @@ nn.Parameter, and the state dict entry {"step", "exp_avg", "exp_avg_sq"} moves t
 
 There is no CPU fallback: without the CUDA library these functions raise.
 """
-import ctypes
 
 import numpy as np
 import torch

@@ -4,7 +4,6 @@ scene/gaussian_model.py:149-175 (six groups, lr per group, eps = 1e-15) and step
 train.py:330-332. State layout (state[p] = {"step", "exp_avg", "exp_avg_sq"}) and param_groups
 are torch's, so the densification code that edits optimizer state by hand
 (scene/gaussian_model.py:258-340) keeps working on it."""
-import ctypes
 
 import torch
 

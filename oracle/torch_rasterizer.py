@@ -10,7 +10,6 @@ rasterizer_impl.cu:70-138 (tile membership, depth order). The reference's backwa
 0.99 clamp, the 1/255 and power>0 skips and the 1e-4 stop as constants (backward.cu:495-503);
 here they are detached masks / straight-through so autograd reproduces exactly that.
 """
-import math
 
 import torch
 

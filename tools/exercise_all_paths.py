@@ -1,5 +1,5 @@
 import sys; sys.path.insert(0, '.')
-import numpy as np, torch
+import torch
 from tests.common import scene_inputs, smooth_dL
 from tests import gpu_common as gc
 inp = scene_inputs(3000, 100, 37, seed=1, bg=(0.2,0.5,0.9))

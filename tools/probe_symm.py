@@ -1,7 +1,6 @@
 """Probe of torch symmetric memory / NVLS multicast on this box (torchrun, >= 2 ranks)."""
 import json
 import os
-import time
 
 import torch
 import torch.distributed as dist
