@@ -18,9 +18,8 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
-# NCCL prints its version banner on stdout at VERSION/INFO level; stdout carries ONE JSON line
-if os.environ.get("E3_KEEP_NCCL_DEBUG") is None:
-    os.environ["NCCL_DEBUG"] = "WARN"
+# NCCL_DEBUG is left as the launcher set it (its INIT lines carry the communicator's rank count); the result
+# is the one line of stdout that starts with '{"metric"' or '{"impl"'
 
 import numpy as np  # noqa: E402
 
@@ -44,6 +43,8 @@ def parse():
                     help="multi-GPU gradient exchange: auto = own NVLS all-reduce kernel from 4 GPUs on when the box supports multicast, else NCCL")
     ap.add_argument("--dropin-no-sync", action="store_true",
                     help="with --path dropin: the opt-in forward without the host read-back of num_rendered (E3_DROPIN_NO_SYNC)")
+    ap.add_argument("--reference-on-cpu", action="store_true",
+                    help="with --impl reference: time the C port on the host cores even if the reference CUDA build is loadable")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=25.0)
@@ -192,8 +193,10 @@ def cpu_arm(scene, steps, warmup, budget_s):
     """Times the oracle; every step is the full per-Gaussian work plus a band of pixel rows of
     the blends, extrapolated to the whole frame (blend cost is proportional to rows)."""
     H = scene["cfg"]["H"]
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    from oracle import raster_oracle as ro
+    # set explicitly: under torch.distributed.run the process inherits OMP_NUM_THREADS=1; `cores` is the
+    # count OpenMP reports back, i.e. the threads really used
+    cores = ro.set_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     deblur = scene["cfg"]["deblur"]
     probe_rows = max(16, (H // 16 // 8) * 16)
     tg, tb = cpu_iteration(scene, (3, 3, 4), probe_rows, deblur)          # calibration (also warms caches)
@@ -225,8 +228,19 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":
-        # the reference's own algorithm on the host cores (oracle port), rank 0 only
+        # rank 0 only. The reference's own implementation of the path: its CUDA sources compiled unmodified for
+        # sm_100a (oracle/_ref) under its render()/loss flow when a GPU and the library are there -- the bar the
+        # north star names; otherwise its algorithm on the host cores (C port of the oracle)
         if rank != 0:
+            return
+        line = None
+        if not args.reference_on_cpu:
+            try:
+                line = reference_cuda_arm(args, cfg_name, world)
+            except Exception as ex:
+                sys.stderr.write("bench.py: reference CUDA build not usable (%r); timing the CPU port instead\n" % (ex,))
+        if line is not None:
+            print(json.dumps(line))
             return
         scene = syn.make_scene(cfg_name, kind=args.kind, P=args.P)
         v, t_iter, cores, sample = cpu_arm(scene, max(1, args.steps), max(1, args.warmup), 150.0)
@@ -462,6 +476,8 @@ def main():
     line["config"]["path"] = path_name
     line["config"]["gradient_exchange"] = exchange_used["kind"]
     line["config"]["num_rendered"] = Rs
+    if world > 1:
+        line["comm"] = {"backend": dist.get_backend(), "nranks": dist.get_world_size()}
     line["mpix_per_sec"] = value * 3 * N / 1e6
     line["config"]["unit_note"] = "one iteration = one event view-pair (3 renders fwd + event loss + bwd); value counts view-pairs per second over all ranks"
     line["e2e"] = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d + cam_bytes), "d2h_bytes_per_step": 4,
@@ -480,14 +496,17 @@ def main():
         per_launch_ms = t_ms / n
         algo = float(np.mean([bytes_bwd_blend(P, r, N, T) for r in Rs]))
         ach = algo / (per_launch_ms * 1e-3) / 1e9
+        # dram__bytes_read.sum + dram__bytes_write.sum and warp instructions per launch come from the committed
+        # ncu --set full capture; the file carries the hash of the kernel source it was captured from and is
+        # ignored (traffic null) once render.cu has changed since
+        tj, traffic_file = load_traffic()
         traffic, traffic_src = None, None
-        try:        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-            if cfg_name == "c3" and "render_bwd_kernel<1>" in tj:
-                traffic = tj["render_bwd_kernel<1>"]["dram_bytes_per_launch"]
-                traffic_src = "profiles/r1_traffic.json (ncu --set full, c3, render_bwd_kernel<1>: the single-channel variant, 2 of the 3 launches per step)"
-        except Exception:
-            pass
+        kname = "render_bwd_kernel<1, 0>" if "render_bwd_kernel<1, 0>" in tj else "render_bwd_kernel<1>"
+        if cfg_name == "c3" and kname in tj:
+            traffic = tj[kname]["dram_bytes_per_launch"]
+            traffic_src = "%s (ncu --set full, c3, %s: the single-channel variant, 2 of the 3 launches per step)" % (traffic_file, kname)
+        elif cfg_name == "c3":
+            traffic_src = "no ncu capture of the current render.cu is committed (stale captures are refused)"
         line["roofline"] = {"bound": "hbm", "kernel": "render_bwd_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                             "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src, "launch_ms": per_launch_ms, "launches": int(n),
                             "algorithmic_bytes_per_launch": algo,
@@ -495,19 +514,24 @@ def main():
                             "note": "the blend kernels are issue/latency bound, not HBM bound; see DESIGN.md"}
         # the blend kernels are issue bound: the second roofline is the warp-instruction rate, with the
         # instruction count per launch taken from the same committed ncu capture
+        wi = None
         try:
-            wi = ((tj["render_bwd_kernel<3>"]["warp_inst_per_launch"] + 2 * tj["render_bwd_kernel<1>"]["warp_inst_per_launch"]) / 3
-                  if cfg_name == "c3" else None)
+            k3 = "render_bwd_kernel<3, 0>" if "render_bwd_kernel<3, 0>" in tj else "render_bwd_kernel<3>"
+            if cfg_name == "c3":
+                wi = (tj[k3]["warp_inst_per_launch"] + 2 * tj[kname]["warp_inst_per_launch"]) / 3
         except Exception:
             wi = None
         if wi and clk and clk.get("sm_mhz"):
             peak_issue = 148 * 4 * clk["sm_mhz"] * 1e6
             line["roofline_issue"] = {"bound": "issue", "kernel": "render_bwd_kernel", "achieved": wi / (per_launch_ms * 1e-3),
                                       "peak": peak_issue, "unit": "warp instructions/s", "frac": wi / (per_launch_ms * 1e-3) / peak_issue,
-                                      "note": "warp instructions per launch from profiles/r1_traffic.json (ncu), mean over the one C=3 and two C=1 launches of a step; launch time live (three concurrent streams share the SMs, so this is a lower bound of the kernel's own rate), peak = 148 SMs x 4 schedulers x SM clock under load"}
+                                      "note": "warp instructions per launch from %s (ncu), mean over the one C=3 and two C=1 launches of a step; launch time live (three concurrent streams share the SMs, so this is a lower bound of the kernel's own rate), peak = 148 SMs x 4 schedulers x SM clock under load" % traffic_file}
     b_iter = sum(bytes_render(P, r, N, T) for r in Rs) + 108 * N + (24 * N if deblur else 0)
-    line["iter_roofline"] = {"algorithmic_bytes": b_iter, "achieved_gbs": b_iter / (ms_per_step * 1e-3) / 1e9,
-                             "frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak}
+    b_step = b_iter * len(my_pairs)          # one step of this GPU = len(my_pairs) view-pairs
+    line["iter_roofline"] = {"algorithmic_bytes_per_pair": b_iter, "pairs_per_gpu_per_step": len(my_pairs),
+                             "achieved_gbs": b_step / (ms_per_step * 1e-3) / 1e9,
+                             "frac": b_step / (ms_per_step * 1e-3) / 1e9 / peak,
+                             "note": "per GPU: B_iter of SURVEY 8d (the reference algorithm's bytes) x the view-pairs this GPU processes per step / step time"}
     line["stages_ms_per_iter"] = stages
     if use_fused:
         # extra (not the headline): the reference's train and event camera lists share their poses
@@ -573,6 +597,110 @@ def main():
         dist.destroy_process_group()
 
 
+def reference_cuda_arm(args, cfg_name, world):
+    """bench.py --impl reference on a GPU box: the UNMODIFIED reference rasterizer (oracle/_ref: forward.cu,
+    backward.cu, rasterizer_impl.cu compiled for sm_100a) under the reference's own flow -- PyTorch activations,
+    eval_sh, render(), the event loss INCLUDING the ssim_gray evaluation it multiplies by 0 (train.py:177-178),
+    loss.backward() -- one view-pair per step on ONE GPU (the reference has no multi-GPU path). None of this
+    repository's kernels run here."""
+    import torch
+    from event_3dgs_b200 import pipeline as pl
+    from event_3dgs_b200 import synthetic as syn
+    from oracle import ref_cuda
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device")
+    if not ref_cuda.available():
+        raise RuntimeError("oracle/_ref/libref_dgr.so not built")
+    ref_cuda.lib()
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    scene = syn.make_scene(cfg_name, kind=args.kind, P=args.P)
+    cfg = scene["cfg"]
+    deblur = cfg["deblur"]
+    pc = pl.GaussianParams(scene["gaussians"], dev)
+    cams = [pl.make_camera(c, dev) for c in scene["cameras"]]
+    gt_dev = {k: torch.as_tensor(v).to(dev) for k, v in scene["gt"].items()}
+    gt_host_u8 = {k: torch.as_tensor(np.round(v * 255.0).astype(np.uint8)).pin_memory() for k, v in scene["gt"].items()
+                  if deblur or k != "blurry"}
+    bg = torch.zeros(3, device=dev)
+    c_param = torch.nn.Parameter(torch.tensor(0.17, device=dev))
+    leaves = pc.leaves() + [c_param]
+    pairs = args.pairs or (64 if cfg_name == "c5" else world)
+
+    def render_ref(cam, pc_, pipe, bg_, **kw):
+        return pl.render(cam, pc_, pipe, bg_, rasterizer_cls=ref_cuda.RefGaussianRasterizer)
+
+    def it(s, gt):
+        v = 2 + (7 * s) % 80
+        for p in leaves:
+            p.grad = None
+        loss, _ = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur, render_fn=render_ref,
+                                     dead_ssim=True)
+        loss.backward()
+        return loss
+
+    def timed(fn, steps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record()
+        for s in range(steps):
+            fn(s)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1), w0, time.time()
+
+    W = max(3, args.warmup)
+    for s in range(W):
+        it(s, gt_dev)
+    clocks = Clocks(dev.index or 0)
+    ms, w0, w1 = timed(lambda s: it(W + s, gt_dev), args.steps)
+    clk = clocks.stop(w0, w1)
+    value = 1e3 / (ms / args.steps)
+
+    def e2e_step(s):
+        # the frames as they are on disk (8-bit) from pinned host memory, /255 on the device as the reference's
+        # loader does on the host (utils/general_utils.py:21-27); loss.item() every iteration (train.py:303)
+        gt = {k: v.to(dev, non_blocking=True).float() / 255.0 for k, v in gt_host_u8.items()}
+        return float(it(W + s, gt).item())
+
+    for s in range(2):
+        e2e_step(s)
+    ms_e, _, _ = timed(e2e_step, args.steps)
+    e2e_value = 1e3 / (ms_e / args.steps)
+    sample = "reference CUDA sources (oracle/_ref, sm_100a) + PyTorch SH / activations / event loss incl. the dead ssim_gray call + " \
+             "autograd, one view-pair per step on one GPU; %d timed steps, host work on 1 thread" % args.steps
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload(cfg, cfg_name, args.kind, pairs),
+            "reference_class": "cuda (the reference's own kernels compiled for sm_100a; it has no multi-GPU path, so it always runs on one GPU)",
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference", "sample": sample},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(sum(v.numel() for v in gt_host_u8.values()) + 3 * 35 * 4),
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e / args.steps},
+            "gpu_launches": 0, "clocks": clk}
+    return line
+
+
+def load_traffic():
+    """Newest profiles/r*_traffic.json whose recorded sha256 of csrc/render.cu equals the current file's
+    (tools/ncu_summary.py stamps it). Returns ({}, None) when none matches: stale counters are not reported."""
+    import glob
+    import hashlib
+    try:
+        cur = hashlib.sha256(open(os.path.join(ROOT, "event_3dgs_b200", "csrc", "render.cu"), "rb").read()).hexdigest()
+    except OSError:
+        return {}, None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic*.json")), reverse=True):
+        try:
+            tj = json.load(open(path))
+        except Exception:
+            continue
+        if tj.get("_source_sha256", {}).get("render.cu") == cur:
+            return tj, os.path.relpath(path, ROOT)
+    return {}, None
+
+
 def last_num_rendered():
     from event_3dgs_b200 import rasterizer
     rasterizer.verify_no_sync(True)
@@ -595,7 +723,7 @@ def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves
         v = view_of(args.warmup + s)
         for p in leaves:
             p.grad = None
-        loss, _ = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur, render_fn=render_ref)
+        loss, _ = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur, render_fn=render_ref, dead_ssim=True)
         loss.backward()
 
     for s in range(3):
@@ -603,7 +731,7 @@ def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves
     steps = max(3, min(args.steps, 10))
     ms, _, _ = timed(it, steps)
     out = {"value": 1e3 / (ms / steps), "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
-           "what": "reference diff-gaussian-rasterization sources compiled for sm_100a (oracle/_ref) + PyTorch SH/loss"}
+           "what": "reference diff-gaussian-rasterization sources compiled for sm_100a (oracle/_ref) + PyTorch SH/loss incl. the ssim_gray evaluation the reference multiplies by 0 (train.py:177-178)"}
     # the reference's whole training step: the same iteration + its densification statistics
     # (train.py:319-320) + torch.optim.Adam on its six groups + Adam(c)
     from event_3dgs_b200 import trainer as tr
@@ -621,7 +749,7 @@ def ref_cuda_leg(pc, cams, gt, c_param, bg, deblur, args, view_of, timed, leaves
 
     def train_it(s):
         v = view_of(args.warmup + s)
-        loss, pkg = pl.event_iteration(pc_r, cams[v], cams[v], cams[v + 1], gt, c_r, bg, deblur=deblur, render_fn=render_ref)
+        loss, pkg = pl.event_iteration(pc_r, cams[v], cams[v], cams[v + 1], gt, c_r, bg, deblur=deblur, render_fn=render_ref, dead_ssim=True)
         loss.backward()
         with torch.no_grad():
             vis, radii, vsp = pkg["visibility_filter"], pkg["radii"], pkg["viewspace_points"]

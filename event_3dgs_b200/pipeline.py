@@ -171,11 +171,16 @@ def l1_loss(network_output, gt):
     return torch.abs((network_output - gt)).mean()
 
 
-def event_loss(image, image_now, image_next, gt_now, gt_next, gt_intensity, c, gt_blur=None):
-    """train.py:165-203 (lambda_dssim is forced to 0 at :177, so the dead ssim_gray call is omitted)."""
+def event_loss(image, image_now, image_next, gt_now, gt_next, gt_intensity, c, gt_blur=None, dead_ssim=False):
+    """train.py:165-203. lambda_dssim is forced to 0 at :177, so the ssim_gray term of :178 contributes
+    nothing; dead_ssim=True still EVALUATES it (and lets autograd walk it) exactly as the reference does --
+    used where the reference's own cost is timed (bench.py --impl reference)."""
     img_diff = differentialable_event_simu(image_now, image_next, False, c)
     gt_image = differentialable_event_simu(gt_now, gt_next, False, 0.17)
     loss1 = l1_loss(img_diff, gt_image)
+    if dead_ssim:
+        lambda_dssim = 0
+        loss1 = (1.0 - lambda_dssim) * loss1 + lambda_dssim * (1.0 - ssim(img_diff, gt_image))
     loss2 = l1_loss(image, gt_intensity)
     Event_weight = 0.9
     mask = (gt_image != 0).float()
@@ -187,7 +192,7 @@ def event_loss(image, image_now, image_next, gt_now, gt_next, gt_intensity, c, g
     return loss
 
 
-def event_iteration(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, render_fn=render, pipe=PIPE):
+def event_iteration(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, render_fn=render, pipe=PIPE, dead_ssim=False):
     """One --event training iteration up to (not including) backward: train.py:144-203.
     gt: dict(intensity, event_now, event_next[, blurry]) of [3,H,W] tensors. Returns (loss, first render pkg)."""
     pkg = render_fn(cam_train, pc, pipe, bg)
@@ -195,7 +200,7 @@ def event_iteration(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, r
     image_now = render_fn(cam_now, pc, pipe, bg)["render"]
     image_next = render_fn(cam_next, pc, pipe, bg)["render"]
     loss = event_loss(image, image_now, image_next, gt["event_now"], gt["event_next"], gt["intensity"], c,
-                      gt["blurry"] if deblur else None)
+                      gt["blurry"] if deblur else None, dead_ssim=dead_ssim)
     return loss, pkg
 
 

@@ -209,6 +209,15 @@ uint32_t orc_get_higher_msb(uint32_t n)
 	return msb;
 }
 
+/* Host threads of the OpenMP loops below: set explicitly by the timing harness (an inherited
+ * OMP_NUM_THREADS=1, torchrun's default, would otherwise silently serialise the CPU baseline). */
+#ifdef _OPENMP
+#include <omp.h>
+int orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); return omp_get_max_threads(); }
+#else
+int orc_set_threads(int n) { (void)n; return 1; }
+#endif
+
 /* rasterizer_impl.cu:54-66 + auxiliary.h:139-164 (markVisible / checkFrustum) */
 void orc_mark_visible(int P, const float* means, const float* vm, const float* pm, unsigned char* present)
 {

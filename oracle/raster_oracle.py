@@ -43,7 +43,10 @@ def _f32(a):
 
 
 def set_threads(n):
+    """Sets the OpenMP thread count of the oracle's loops (omp_set_num_threads) and returns the count in
+    effect; the environment variable alone is read once when libgomp loads and may have been inherited."""
     os.environ["OMP_NUM_THREADS"] = str(n)
+    return int(lib().orc_set_threads(int(n)))
 
 
 def get_higher_msb(n):

@@ -18,3 +18,17 @@ def cuda_dev():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """Measured parity errors of the -m gpu run (tests/common.observe) -> gpurun_out/parity_observed.json."""
+    try:
+        import json
+        from tests import common
+        if common.OBSERVED:
+            out = os.path.join(ROOT, "gpurun_out")
+            os.makedirs(out, exist_ok=True)
+            with open(os.path.join(out, "parity_observed.json"), "w") as f:
+                json.dump(common.OBSERVED, f, indent=1, sort_keys=True)
+    except Exception:
+        pass

@@ -46,6 +46,12 @@ def main(path, out_json=None):
         out[short] = {"launches": len(a["time"]), "dram_bytes_per_launch": m["dram_rd"] + m["dram_wr"], "time_us": m["time"],
                       "warp_inst_per_launch": m["inst"], "issue_active_pct": m["issue_pct"]}
     if out_json:
+        # bench.py only trusts these counters while the kernel sources are the ones that were profiled
+        import hashlib
+        import os
+        csrc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "event_3dgs_b200", "csrc")
+        out["_source_sha256"] = {f: hashlib.sha256(open(os.path.join(csrc, f), "rb").read()).hexdigest()
+                                 for f in ("render.cu", "binning.cu", "preprocess.cu", "common.cuh")}
         json.dump(out, open(out_json, "w"), indent=1)
 
 
