@@ -12,7 +12,10 @@
 // Per-Gaussian gradient accumulator written by the backward blend and consumed by the
 // backward preprocess: 12 floats (48 B, 16-byte aligned) so that one warp's reduced values
 // land in one or two 32-byte sectors.
-//   0,1 dL/dmean2D (x,y)   2,3,4 dL/dconic (xx,xy,yy)   5 dL/dopacity   6.. dL/dcolour
+// The blend leaves sums that lack their per-Gaussian factors (g = G dL/dalpha, d = centre - pixel):
+//   0 sum g   1,2 -sum g dpower/ddx, -g dpower/ddy   3,4,5 sum g dx^2, g dx dy, g dy^2   6,7,8 dL/dcolour
+//   9,10 -sum g dpower/ddx, -g dpower/ddy of the second seed (dual backward blend)
+// and the backward preprocess finishes them (preprocess.cu).
 #define E3_ACC_STRIDE 12
 
 static inline size_t e3_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

@@ -477,7 +477,8 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	float tan_fovx, float tan_fovy, float* __restrict__ acc,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
-	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot, long long mc, bool mean2d_second)
+	float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot, long long mc, bool mean2d_second,
+	const float4* __restrict__ rec, int W, int H)
 {
 	constexpr int BT = E3_PB_THREADS;
 	extern __shared__ __align__(16) float smem[];
@@ -497,7 +498,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	// Gaussian turns out to be visible: one round trip to memory instead of a chain of
 	// dependent ones (the kernel is latency bound, not bandwidth bound).
 	int rad = 0;
-	float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, a2 = a0;
+	float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, a2 = a0, rc1 = a0;
 	float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
 	float opac_raw = 0.f;
 	uint8_t cl[3] = { 0, 0, 0 };
@@ -505,6 +506,7 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 	if (live) {
 		rad = radii[idx];
 		a0 = a4[0]; a1 = a4[1]; a2 = a4[2];
+		rc1 = __ldg(rec + 3 * idx + 1);
 		if (scales) q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
 		if (RAW) opac_raw = __ldg(opacities_raw + idx);
 		if (shs) { cl[0] = clamped[3 * idx]; cl[1] = clamped[3 * idx + 1]; cl[2] = clamped[3 * idx + 2]; }
@@ -525,6 +527,20 @@ __global__ void __launch_bounds__(E3_PB_THREADS) preprocess_bwd_kernel(
 		a4[0] = a4[1] = a4[2] = make_float4(0.f, 0.f, 0.f, 0.f);
 	} else {
 		a0 = a1 = a2 = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
+	if (vis) {      // (the record of a culled Gaussian was never written)
+		// The backward blend leaves sums that lack their per-Gaussian factors (g = G dL/dalpha, d = centre - pixel):
+		//   a0 = {sum g, -sum g dpower/ddx, -sum g dpower/ddy, sum g dx^2}  a1 = {sum g dx dy, sum g dy^2, dL/dc0, dL/dc1}
+		//   a2 = {dL/dc2, second seed's -sum g dpower/ddx, -sum g dpower/ddy, -}
+		// With dL/dG = opacity g this is backward.cu:538-554: dL/dmean2D = dL/dG dG/ddel (0.5 W, 0.5 H),
+		// dL/dconic = -0.5 G d d^T dL/dG, dL/dopacity = sum g.
+		// From here on a0 = {dL/dmean2D.x, .y, dL/dconic.xx, .xy}, a1 = {dL/dconic.yy, dL/dopacity, ..}, a2.yz = second seed's dL/dmean2D.
+		const float o = rc1.y;
+		const float sw = -0.5f * (float)W * o, sh = -0.5f * (float)H * o, sc = -0.5f * o;
+		const float sum_g = a0.x;
+		a0 = make_float4(sw * a0.y, sh * a0.z, sc * a0.w, sc * a1.x);
+		a1 = make_float4(sc * a1.y, sum_g, a1.z, a1.w);
+		a2.y *= sw; a2.z *= sh;
 	}
 	const float3 mean = make_float3(s_mean[3 * t], s_mean[3 * t + 1], s_mean[3 * t + 2]);
 	float c3[6];
@@ -776,7 +792,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	kern<<<grid, BT, sm, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
-	dL_dscale, dL_drot, (AC) ? f.mc_delta : 0ll, f.mean2d_from_second_seed); } while (0)
+	dL_dscale, dL_drot, (AC) ? f.mc_delta : 0ll, f.mean2d_from_second_seed, g.rec, f.W, f.H); } while (0)
 	if (raw && f.C == 1) {
 		if (shrest) { if (accumulate) LAUNCH(1, true, true, true); else LAUNCH(1, true, false, true); }
 		else { if (accumulate) LAUNCH(1, true, true, false); else LAUNCH(1, true, false, false); }

@@ -32,6 +32,7 @@ namespace {
 // for finished tiles at every batch. The backward has no early exit and gains from fewer barriers (18 % of
 // its warp cycles wait at them: the warps of a tile do different amounts of work per batch).
 constexpr int kBatchF = E3_BLEND_BATCH_FWD, kBatchB = E3_BLEND_BATCH_BWD;
+constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ void pixel_of_thread(int& lx, int& ly)
 {
@@ -278,30 +279,25 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 #pragma unroll
 	for (int i = 0; i < 8; i++) total = max(total, s_max[i]);
 
-	float dL_dpixel[C], accum_rec[C], last_color[C];
+	// Bp = sum_c dL/dpixel_c * (colour seen behind the current instance, normalised by the transmittance in
+	// front of what lies behind): the background to start with. With pc = sum_c dL/dpixel_c colour_c this is
+	// backward.cu:505-534 (accum_rec recurrence + background term) pre-multiplied with dL/dpixel:
+	//   dL/dalpha_i = T_i (pc_i - Bp);   Bp <- Bp + alpha_i (pc_i - Bp)
+	float dL_dpixel[C], dL_dpixel2[C];
 	const size_t HW = (size_t)H * W;
-	float bg_dot_dpixel = 0.f;
+	float Bp = 0.f, Bp2 = 0.f;
 #pragma unroll
 	for (int c = 0; c < C; c++) {
 		dL_dpixel[c] = inside ? dL_dpixels[c * HW + pix_id] : 0.f;
-		accum_rec[c] = 0.f; last_color[c] = 0.f;
-		bg_dot_dpixel += __ldg(bg + c) * dL_dpixel[c];
-	}
-	float dL_dpixel2[C];
-	float bg_dot_dpixel2 = 0.f;
-#pragma unroll
-	for (int c = 0; c < C; c++) {
 		dL_dpixel2[c] = (DUAL && inside) ? dL_dpixels2[c * HW + pix_id] : 0.f;
-		bg_dot_dpixel2 += __ldg(bg + c) * dL_dpixel2[c];
+		const float b = __ldg(bg + c);
+		Bp += b * dL_dpixel[c];
+		Bp2 += b * dL_dpixel2[c];
 	}
-	float last_alpha = 0.f;
-	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask), aId = smem_addr(sId);
 	// after warp_reduce8 lane L with (L & 3) == 0 holds slot my_slot of the accumulator row
 	const int my_slot = DUAL ? ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1)
 		: ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-	const float slot_scale = (my_slot == 0 || my_slot == 9) ? ddelx_dx : (my_slot == 1 || my_slot == 10) ? ddely_dy
-		: (my_slot >= 2 && my_slot < 5) ? -0.5f : 1.0f;
 
 	// instance index within the tile's list, walked from total-1 down to 0; an instance with
 	// 0-based index i has contributor number i (reference: `contributor--` before the test,
@@ -337,11 +333,13 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const float4 a = lds_f4(aAB + 32 * j);
 			const float4 b = lds_f4(aAB + 32 * j + 16);
 			const float dx = a.x - pixfx, dy = a.y - pixfy;
+			// the forward's own rounding of the power: for a thin, oblique ellipse its terms cancel to a small
+			// difference, and another evaluation order would give another G than the one the forward blended with
 			const float power = eval_power(dx, dy, a.z, a.w, b.x);
 			// ex2.approx of power * log2(e): within 5e-7 relative of the forward's accurate expf, far inside
 			// the gradient tolerance (1e-4), 6 instructions shorter per examined pair
 			float G;
-			asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * 1.4426950408889634f));
+			asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
 			float alpha = fminf(0.99f, b.y * G);
 			// contributor = total - 1 - (b0 + j) < last_contributor  <=>  j > jlim
 			const bool valid = (j > jlim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
@@ -354,52 +352,49 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			G = valid ? G : 0.f;
 			float v[8];
 			float v8 = 0.f;
-			// one reciprocal serves both divisions of backward.cu:503,534 (tolerance-checked path;
-			// rcp.approx is within 1 ulp and 1 - alpha lies in [0.01, 1], no special cases)
+			// one reciprocal serves the division of backward.cu:503 (tolerance-checked path; rcp.approx is
+			// within 1 ulp and 1 - alpha lies in [0.01, 1], no special cases)
 			float ra;
 			asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(1.f - alpha));
 			T = T * ra;
-			const float dchannel_dcolor = alpha * T;
-			float col[3];
-			col[0] = b.z; col[1] = b.w; col[2] = (C == 3) ? lds_f(aC + 4 * j) : 0.f;
-			float dL_dalpha = 0.0f, dL_dalpha2 = 0.0f;
-#pragma unroll
-			for (int c = 0; c < C; c++) {
-				const float ar = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
-				accum_rec[c] = valid ? ar : accum_rec[c];
-				last_color[c] = valid ? col[c] : last_color[c];
-				dL_dalpha += (col[c] - ar) * dL_dpixel[c];
-				if (DUAL) dL_dalpha2 += (col[c] - ar) * dL_dpixel2[c];
+			const float aT = alpha * T;
+			float pc = dL_dpixel[0] * b.z, pc2 = dL_dpixel2[0] * b.z, c2v = 0.f;
+			if (C == 3) {
+				c2v = lds_f(aC + 4 * j);
+				pc = fmaf(dL_dpixel[2], c2v, fmaf(dL_dpixel[1], b.w, pc));
+				if (DUAL) pc2 = fmaf(dL_dpixel2[2], c2v, fmaf(dL_dpixel2[1], b.w, pc2));
 			}
-			dL_dalpha *= T;
-			last_alpha = valid ? alpha : last_alpha;
-			dL_dalpha += (-T_final * ra) * bg_dot_dpixel;
-			if (DUAL) dL_dalpha2 = dL_dalpha2 * T + (-T_final * ra) * bg_dot_dpixel2;
-			const float dL_dG = b.y * dL_dalpha;
-			const float gdx = G * dx, gdy = G * dy;
-			const float dG_ddelx = -gdx * a.z - gdy * a.w;
-			const float dG_ddely = -gdy * b.x - gdx * a.w;
-			// the constant factors (0.5 W, 0.5 H on the mean, -0.5 on the conic) are applied once, after the
-			// warp reduction, by the lane that writes the slot (slot_scale)
-			v[0] = dL_dG * dG_ddelx;
-			v[1] = dL_dG * dG_ddely;
-			v[2] = gdx * dx * dL_dG;
-			v[3] = gdx * dy * dL_dG;
-			v[4] = gdy * dy * dL_dG;
-			v[5] = G * dL_dalpha;
-			v[6] = dchannel_dcolor * dL_dpixel[0];
+			const float dB = pc - Bp;
+			const float g = G * (dB * T);                      // G dL/dalpha; dL/dG = opacity * g
+			Bp = fmaf(alpha, dB, Bp);                          // alpha = 0 (no contribution) leaves it alone
+			// What leaves the warp are sums that still lack their per-Gaussian factors (d = centre - pixel):
+			//   sum g, -sum g dpower/ddx, -sum g dpower/ddy, sum g dx^2, sum g dx dy, sum g dy^2, sum alpha T dL/dpixel_c.
+			// The backward preprocess, which has the opacity at hand, turns them into dL/dmean2D, dL/dconic and
+			// dL/dopacity (backward.cu:538-554). The derivative of the power is formed per pixel, not from first
+			// moments after the sum: along the major axis of a thin ellipse conic.x dx + conic.y dy cancels.
+			const float gxv = g * dx, gyv = g * dy;
+			v[0] = g;
+			v[1] = fmaf(gxv, a.z, gyv * a.w);                  // g (conic.x dx + conic.y dy) = -g dpower/ddx
+			v[2] = fmaf(gyv, b.x, gxv * a.w);                  // g (conic.z dy + conic.y dx) = -g dpower/ddy
+			v[3] = gxv * dx;
+			v[4] = gxv * dy;
+			v[5] = gyv * dy;
+			v[6] = aT * dL_dpixel[0];
 			v[7] = 0.f;
-			if (C == 3) { v[7] = dchannel_dcolor * dL_dpixel[1]; v8 = dchannel_dcolor * dL_dpixel[2]; }
+			if (C == 3) { v[7] = aT * dL_dpixel[1]; v8 = aT * dL_dpixel[2]; }
 			if (DUAL) {
-				const float dL_dG2 = b.y * dL_dalpha2;
+				const float dB2 = pc2 - Bp2;
+				const float g2 = G * (dB2 * T);
+				Bp2 = fmaf(alpha, dB2, Bp2);
 				float u[16];
 #pragma unroll
 				for (int i = 0; i < 8; i++) u[i] = v[i];
-				u[8] = v8; u[9] = dL_dG2 * dG_ddelx; u[10] = dL_dG2 * dG_ddely;
+				const float g2x = g2 * dx, g2y = g2 * dy;
+				u[8] = v8; u[9] = fmaf(g2x, a.z, g2y * a.w); u[10] = fmaf(g2y, b.x, g2x * a.w);
 				u[11] = u[12] = u[13] = u[14] = u[15] = 0.f;
 				warp_reduce16(u, lane);
 				if ((lane & 1) == 0 && my_slot < 11)
-					atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + my_slot, u[0] * slot_scale);
+					atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + my_slot, u[0]);
 				continue;
 			}
 			warp_reduce8(v, lane);
@@ -409,7 +404,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			}
 			if ((lane & 3) == 0) {
 				float* dst = acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE;
-				if (C == 3 || my_slot < 7) atomicAdd(dst + my_slot, v[0] * slot_scale);
+				if (C == 3 || my_slot < 7) atomicAdd(dst + my_slot, v[0]);
 			}
 			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + 8, v8);
 		}

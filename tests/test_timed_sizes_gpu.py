@@ -55,11 +55,15 @@ def test_dropin_bit_exact_vs_reference_cuda_at_timed_sizes(gc, name, P, W, H, ki
     # its sibling gradient instead of against rounding noise
     fl = {k: 0.0 for k in KEYS}
     fl["dL_drotations"] = 1e-3 * float(gr["dL_dscales"].abs().max()) * float(np.abs(inp["scales"]).max())
+    gr2 = ref.backward(gc.T(dL))          # the reference against itself: its float atomics commit in another order
+    g2 = gc.ours_backward(fw, inp, dL)
     for k in KEYS:
         a, b = _np(g[k]), _np(gr[k]).reshape(_np(g[k]).shape)
         assert np.isfinite(a).all(), k
+        observe("ref_vs_ref/%s/%s" % (name, k), rel_err(_np(gr2[k]).reshape(a.shape), b, fl[k]))
+        observe("ours_vs_ours/%s/%s" % (name, k), rel_err(_np(g2[k]), a, fl[k]))
         e = observe("dropin_vs_ref/%s/%s" % (name, k), rel_err(a, b, fl[k]))
-        assert e < grad_tol(k, two_atomic_runs=True), (k, e)
+        assert e < grad_tol(k, two_atomic_runs=True, size=name), (k, e)
     culled = ~(fw["radii"] > 0)
     for k in KEYS:
         assert (g[k][culled] == 0).all()
@@ -117,15 +121,25 @@ def test_fused_iteration_vs_reference_route_at_timed_sizes(gc, cfg_name):
             assert e <= IMG_TOL, (tag, call, e)
             # the activations run in-kernel here and as ATen ops there: a borderline radius may differ
             assert observe(key + "radii_mismatch", (pkg["radii"] != radii_ref).float().mean().item()) < 1e-4
-            assert observe(key + "image", rel_err(_np(pkg["render"]), _np(img_ref))) < IMG_TOL
+            # ... and then an alpha >= 1/255 or T < 1e-4 decision of single (pixel, Gaussian) pairs: almost every pixel
+            # agrees to fp32 rounding, an isolated flipped pair moves its pixel by at most ~alpha = 1/255 of a colour
+            d = (pkg["render"] - img_ref).abs()
+            assert observe(key + "image_pixels_off", (d > IMG_TOL * float(img_ref.abs().max())).float().mean().item()) < 1e-4
+            assert observe(key + "image", float(d.max()) / float(img_ref.abs().max())) < 5e-3
+            # rows of the (at most a handful of) Gaussians whose visibility itself differs between the two activation
+            # routes are not comparable -- present in one render, absent from the other; every other row is held
+            same = _np(pkg["radii"] == radii_ref)
             for n, p in zip(names, leaves):
                 if n == "features_rest" and pc.active_sh_degree == 0:
                     assert not p.grad.any() and not g_ref[n].any()
                     continue
-                e = observe(key + n, rel_err(_np(p.grad), g_ref[n], 1e-30))
+                a, b = _np(p.grad), g_ref[n]
+                if a.ndim and a.shape[0] == same.shape[0]:
+                    a, b = a[same], b[same]
+                e = observe(key + n, rel_err(a, b, 1e-30))
                 assert e < grad_tol(n, two_atomic_runs=True), (tag, call, n, e)
-            e = observe(key + "viewspace", rel_err(_np(pkg["viewspace_points"].grad), vs_ref))
-            assert e < GRAD_TOL, (tag, call, e)
+            e = observe(key + "viewspace", rel_err(_np(pkg["viewspace_points"].grad)[same], vs_ref[same]))
+            assert e < GRAD_TOL, (tag, call, "viewspace", e)
     assert len(pkg["num_rendered"]) == 2       # the last variant rendered the shared view once
 
 
