@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
 			ext_y = sqrtf(2.0f * tau * cov.z) * 1.0005f + 0.02f;
 		}
 		rec[3 * idx + 1] = make_float4(conic.z, opac, col[0], col[1]);
-		rec[3 * idx + 2] = make_float4(col[2], ext_x, ext_y, 0.f);
+		rec[3 * idx + 2] = make_float4(col[2], ext_x, ext_y, tau);
 		if (RAW) {
 			// Fused path only (its instance lists are not observable): the reference's rect comes
 			// from the 3-sigma radius, but a pixel is touched only inside the { alpha >= 1/255 } box

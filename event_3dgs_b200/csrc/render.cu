@@ -43,10 +43,16 @@ __device__ __forceinline__ void pixel_of_thread(int& lx, int& ly)
 
 // Which of the tile's eight 8x4 warp blocks can an instance touch at all? A pixel receives a
 // contribution only if alpha = opacity * exp(power) >= 1/255, i.e. inside the ellipse
-// power >= -ln(255 * opacity); (hx, hy) is the half-extent of that ellipse's bounding box,
-// precomputed per Gaussian with a safety margin (preprocess.cu). Bit w = (row r)*2 + (column c)
-// matches pixel_of_thread(). The test is conservative, so skipping changes no result bit.
-__device__ __forceinline__ uint32_t subtile_mask(float x, float y, float hx, float hy)
+// q(d) = conic.x dx^2 + 2 conic.y dx dy + conic.z dy^2 <= 2 tau, tau = ln(255 * opacity) (+ margin), all
+// precomputed per Gaussian (preprocess.cu): (hx, hy) is the half-extent of the ellipse's bounding box.
+// Two steps: the bounding box against the block, then -- for the blocks that pass -- the exact minimum of q over
+// the block's rectangle of pixel centres: 0 if the centre lies inside, otherwise attained on one of the (at most
+// two) faces that look at the centre, where it is a clamped one-dimensional minimisation. The second step removes
+// the blocks that only a corner of the bounding box reaches (about one examined (block, instance) pair in six).
+// Bit w = (row r)*2 + (column c) matches pixel_of_thread(). Both steps are conservative (margins cover the fp32
+// rounding of the blend's own power evaluation; anything odd -- NaN, indefinite conic -- keeps the block), so
+// skipping changes no result bit: the per-pixel test would have skipped the same pairs.
+__device__ __forceinline__ uint32_t subtile_mask(float x, float y, float hx, float hy, float cx, float cy, float cz, float tau)
 {
 	if (!(hx >= 0.f)) return 0u;
 	const float xl = x - hx, xh = x + hx, yl = y - hy, yh = y + hy;
@@ -55,7 +61,35 @@ __device__ __forceinline__ uint32_t subtile_mask(float x, float y, float hx, flo
 #pragma unroll
 	for (int r = 0; r < 4; r++)
 		if ((yh >= 4.f * r) & (yl <= 4.f * r + 3.f)) m |= cm << (2 * r);
-	return m;
+	if (m == 0u) return 0u;
+	const float ry = __fdividef(-cy, cz), rx = __fdividef(-cy, cx), cy2 = cy + cy;
+	const float thr = 2.002f * tau + 2e-3f;
+	uint32_t out = 0;
+#pragma unroll
+	for (int c = 0; c < 2; c++) {
+		const float X0 = 8.f * c - x, X1 = X0 + 7.f;          // pixel centre minus Gaussian centre
+		const float xc = fminf(fmaxf(0.f, X0), X1);
+		const float xm = fmaxf(fabsf(X0), fabsf(X1));
+#pragma unroll
+		for (int r = 0; r < 4; r++) {
+			if (!((m >> (2 * r + c)) & 1u)) continue;
+			const float Y0 = 4.f * r - y, Y1 = Y0 + 3.f;
+			const float yc = fminf(fmaxf(0.f, Y0), Y1);
+			const float ym = fmaxf(fabsf(Y0), fabsf(Y1));
+			const float yy = fminf(fmaxf(ry * xc, Y0), Y1);     // face dx = xc
+			const float xx = fminf(fmaxf(rx * yc, X0), X1);     // face dy = yc
+			float q1 = xc * fmaf(cx, xc, cy2 * yy) + cz * yy * yy;
+			float q2 = xx * fmaf(cx, xx, cy2 * yc) + cz * yc * yc;
+			q1 = xc != 0.f ? q1 : 3.0e38f;
+			q2 = yc != 0.f ? q2 : 3.0e38f;
+			float q = fminf(q1, q2);
+			q = (xc == 0.f && yc == 0.f) ? 0.f : q;
+			// the blend evaluates the power with a few ulp of its largest term
+			const float slack = 4e-6f * fmaf(cx, xm * xm, cz * ym * ym);
+			if (!(q > thr + slack)) out |= 1u << (2 * r + c);
+		}
+	}
+	return out;
 }
 
 // Shared-memory reads through an explicit 32-bit shared address, computed once per thread. With
@@ -141,9 +175,10 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 				const float4 a = __ldg(r);
 				const float4 e = __ldg(r + 2);     // c2, hx, hy, -
 				sAB[2 * l] = a;
-				sAB[2 * l + 1] = __ldg(r + 1);
 				if (C == 3) sC[l] = e.x;
-				sMask[l] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
+				const float4 b = __ldg(r + 1);
+				sAB[2 * l + 1] = b;
+				sMask[l] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z, a.z, a.w, b.x, e.w);
 			}
 		}
 		__syncthreads();
@@ -313,10 +348,11 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 				const float4 a = __ldg(r);
 				const float4 e = __ldg(r + 2);
 				sId[l] = id;
+				const float4 b = __ldg(r + 1);
 				sAB[2 * l] = a;
-				sAB[2 * l + 1] = __ldg(r + 1);
+				sAB[2 * l + 1] = b;
 				if (C == 3) sC[l] = e.x;
-				sMask[l] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z);
+				sMask[l] = (uint8_t)subtile_mask(a.x - tile_x0, a.y - tile_y0, e.y, e.z, a.z, a.w, b.x, e.w);
 			}
 		}
 		__syncthreads();
