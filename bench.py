@@ -318,8 +318,10 @@ def main():
         for k, b in enumerate(my_pairs):
             v = view_of(step, b)
             if use_fused:
+                # lazy_check: num_rendered of a step is read (and checked against the workspace capacity) two steps
+                # later; drain_workspace() below verifies that no timed step had exceeded it
                 l = fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur,
-                                                   gt_ready=gt_ready if k == 0 else None, accumulate=k > 0)
+                                                   gt_ready=gt_ready if k == 0 else None, accumulate=k > 0, lazy_check=True)
             else:
                 l, pkg = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur)
                 l.backward()              # autograd accumulates into .grad over the pairs
@@ -401,6 +403,12 @@ def main():
     ms_per_step = ms / args.steps
     value = pairs * 1e3 / ms_per_step
 
+    def drain_workspace():
+        ws = getattr(pc, "_e3_ws", None)
+        if use_fused and ws is not None:
+            ws.drain()                   # raises if a step overflowed its instance buffers (results would be incomplete)
+    drain_workspace()
+
     # ---- (2) end to end through the public API with host buffers ----
     cam_bytes = 3 * (16 + 16 + 3) * 4
 
@@ -450,6 +458,7 @@ def main():
     torch.cuda.synchronize()
     seen.clear()
     ms_e2e, _, _ = timed(e2e_run, args.steps)
+    drain_workspace()
     assert len(seen) == args.steps and all(np.isfinite(seen)), "every step's loss must have been read"
     e2e_value = pairs * 1e3 / (ms_e2e / args.steps)
 
@@ -539,7 +548,7 @@ def main():
         # same view; rendering it once is loss- and gradient-equivalent (fused.same_view)
         def it_dedupe(s):
             v = view_of(args.warmup + s)
-            fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt_dev, c_param, bg, deblur=deblur, dedupe_views=True)
+            fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt_dev, c_param, bg, deblur=deblur, dedupe_views=True, lazy_check=True)
         for s in range(3):
             it_dedupe(s)
         ms_d, _, _ = timed(it_dedupe, args.steps)

@@ -6,9 +6,25 @@
 
 #include <cstdio>
 #include <mutex>
+#include <set>
+#include <utility>
 #include <vector>
 
-unsigned long long g_e3_launches = 0;
+std::atomic<unsigned long long> g_e3_launches{0};
+
+cudaError_t e3_allow_dynamic_smem_impl(const void* kernel, size_t bytes)
+{
+	static std::mutex mu;
+	static std::set<std::pair<const void*, int>> done;
+	int dev = 0;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) return e;
+	std::lock_guard<std::mutex> l(mu);
+	if (done.count({ kernel, dev })) return cudaSuccess;
+	e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+	if (e == cudaSuccess) done.insert({ kernel, dev });
+	return e;
+}
 
 namespace {
 
@@ -86,7 +102,7 @@ const char* e3_error_string(int code)
 	case E3_ERR_ALLOC_FAILED: return "event3dgs: workspace allocation callback returned NULL";
 	case E3_ERR_PREFILTERED: return "Point is filtered although prefiltered is set. This shouldn't happen!";
 	case E3_ERR_UNSUPPORTED: return "For non-RGB, provide precomputed Gaussian colors!";
-	case E3_ERR_TOO_LARGE: return "event3dgs: input larger than this entry point's fixed capacity (e3_exclusive_scan_noalloc: at most 16777216 values)";
+	case E3_ERR_TOO_LARGE: return "event3dgs: input larger than this entry point's fixed capacity (e3_exclusive_scan_noalloc: 16777216 values; e3_densify_plan: 2^30 rows)";
 	}
 	if (code > 0) return cudaGetErrorString((cudaError_t)code);
 	return "event3dgs: unknown error";
@@ -476,6 +492,17 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	ViewStreams* vs = nullptr;
 	E3_CHECK(view_streams(&vs));
 	cudaStream_t sts[3] = { main_st, vs->side[0], vs->side[1] };
+	// Whatever way this call ends, the caller's stream is ordered behind everything the side streams were given:
+	// after an error return the caller may free or reuse the workspace, seed and gradient buffers on its stream.
+	struct JoinSideStreams {
+		ViewStreams* v; cudaStream_t m; bool armed = true;
+		~JoinSideStreams()
+		{
+			if (!armed) return;
+			for (int k = 0; k < 2; k++)
+				if (cudaEventRecord(v->join[k], v->side[k]) == cudaSuccess) cudaStreamWaitEvent(m, v->join[k], 0);
+		}
+	} join_guard{ vs, main_st };
 	// ---- three forwards, one stream each ----
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
@@ -536,6 +563,7 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 		E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
 		E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
 	}
+	join_guard.armed = false;
 	return 0;
 }
 
@@ -573,7 +601,7 @@ int e3_dist2(int P, const float* points, float* mean_dist2, void* scratch, size_
 	return 0;
 }
 
-unsigned long long e3_kernel_launches(void) { return g_e3_launches; }
+unsigned long long e3_kernel_launches(void) { return g_e3_launches.load(); }
 
 int e3_profile_enable(unsigned stage_mask)
 {

@@ -2,6 +2,7 @@
 #pragma once
 #include <cstdint>
 #include <cstddef>
+#include <atomic>
 #include <cuda_runtime.h>
 
 #define E3_TILE_X 16
@@ -123,7 +124,16 @@ struct E3BinState {
 };
 
 // number of kernels this library has launched (bench.py reports it as gpu_launches)
-extern unsigned long long g_e3_launches;
+extern std::atomic<unsigned long long> g_e3_launches;
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device setting: done once per (kernel, device), with
+// the launching device current (a process may drive several GPUs from several threads).
+cudaError_t e3_allow_dynamic_smem_impl(const void* kernel, size_t bytes);      // api.cu
+template <typename K>
+static inline cudaError_t e3_allow_dynamic_smem(K kernel, size_t bytes)
+{
+	return e3_allow_dynamic_smem_impl(reinterpret_cast<const void*>(kernel), bytes);
+}
 
 // ---- internal launchers (defined in the .cu files) ----
 struct E3Frame {

@@ -743,14 +743,10 @@ cudaError_t e3_launch_preprocess(const E3Frame& f, const float* means3D, const f
 	const int grid = (f.P + 255) / 256;
 	const size_t dyn = (raw && f.D > 0) ? (size_t)256 * 45 * sizeof(float) : 0;
 	if (dyn) {
-		static bool attr_set = false;
-		if (!attr_set) {
-			cudaError_t ea = cudaFuncSetAttribute(preprocess_fwd_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-			if (ea != cudaSuccess) return ea;
-			ea = cudaFuncSetAttribute(preprocess_fwd_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-			if (ea != cudaSuccess) return ea;
-			attr_set = true;
-		}
+		cudaError_t ea = e3_allow_dynamic_smem(preprocess_fwd_kernel<3, true>, dyn);
+		if (ea != cudaSuccess) return ea;
+		ea = e3_allow_dynamic_smem(preprocess_fwd_kernel<1, true>, dyn);
+		if (ea != cudaSuccess) return ea;
 	}
 #define LAUNCH(CH, RW) preprocess_fwd_kernel<CH, RW><<<grid, 256, dyn, st>>>(f.P, f.D, f.M, means3D, scales, f.scale_modifier, \
 	rotations, opacities, shs, f_rest, cov3D_precomp, colors_precomp, viewmatrix, projmatrix, cam_pos, f.W, f.H, \
@@ -787,8 +783,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 #define LAUNCH(CH, RW, AC, SR) do { \
 	auto kern = preprocess_bwd_kernel<CH, RW, AC, SR>; \
 	const size_t sm = SR ? smem_big : smem_small; \
-	static bool attr_set = false; \
-	if (SR && !attr_set) { cudaError_t ea = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); if (ea != cudaSuccess) return ea; attr_set = true; } \
+	if (SR) { cudaError_t ea = e3_allow_dynamic_smem(kern, sm); if (ea != cudaSuccess) return ea; } \
 	kern<<<grid, BT, sm, st>>>(f.P, f.D, f.M, means3D, radii, shs, f_rest, d_frest, \
 	opacities_raw, g.clamped, scales, rotations, f.scale_modifier, cov3D_precomp, g.cov3D, viewmatrix, projmatrix, campos, f.focal_x, \
 	f.focal_y, f.tan_fovx, f.tan_fovy, g.acc, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \

@@ -39,14 +39,21 @@ class Workspace:
         self.r_host = torch.zeros(slots, 2, dtype=torch.int32).pin_memory()
         self.events = [torch.cuda.Event() for _ in range(slots)]
         self.used = [False] * slots
-        # single-call iteration (e3_event_iteration): seeds, loss scratch, one event after the forwards
+        # single-call iteration (e3_event_iteration): seeds, loss scratch, and -- twice, used alternately -- the
+        # pinned words the forwards' num_rendered arrive in and one event after the forwards
         self.seeds = {}
         self.loss_scratch = torch.empty(8, dtype=torch.float64, device=device)
-        self.fw_event = torch.cuda.Event()
+        self.r_host2 = torch.zeros(2, 3, 2, dtype=torch.int32).pin_memory()
+        self.fw_events = [torch.cuda.Event(), torch.cuda.Event()]
         with torch.cuda.device(device):
-            self.fw_event.record(torch.cuda.current_stream(device))      # creates the underlying cudaEvent_t
+            for e in self.fw_events:
+                e.record(torch.cuda.current_stream(device))      # creates the underlying cudaEvent_t
         self.args = _lib.EventIterationArgs()
-        self.pending_single = False
+        self.parity = 0
+        self.pending = [False, False]
+        self.cap_used = [0, 0]           # capacity the iteration of each buffer set was enqueued with
+        self.last_Rs = None
+        self.overflows = 0
         self.resize(cap)
 
     def resize(self, cap):
@@ -68,10 +75,6 @@ class Workspace:
         and backward kernels in the stream, so this does not drain the pipeline). Returns the
         measured R per slot; raises Overflow after enlarging the buffers if one exceeded cap."""
         Rs, worst = [], 0
-        if self.pending_single:
-            self.fw_event.synchronize()
-            self.pending_single = False
-            Rs = [int(self.r_host[k, 0]) for k in range(3)]
         for k in range(self.slots):
             if self.used[k]:
                 self.events[k].synchronize()
@@ -82,6 +85,38 @@ class Workspace:
             self.resize(int(worst * 1.5))
             raise Workspace.Overflow(worst)
         return Rs
+
+    def harvest(self, par):
+        """Single-call iterations: wait for the forwards of the iteration that used buffer set `par` (they precede
+        its loss and backward kernels in the stream) and read their num_rendered. Raises Overflow after enlarging
+        the binning buffers if one exceeded the capacity, and enlarges them ahead of need above 85 % of it."""
+        self.fw_events[par].synchronize()
+        self.pending[par] = False
+        Rs = [int(self.r_host2[par, k, 0]) for k in range(3)]
+        self.last_Rs = Rs
+        worst = max(Rs)
+        if worst > self.cap_used[par]:
+            self.overflows += 1
+            if worst > self.cap:
+                self.resize(int(worst * 1.5))
+            raise Workspace.Overflow(worst)
+        if worst > 0.85 * self.cap:
+            self.resize(int(worst * 1.3) + 4096)
+        return Rs
+
+    def drain(self):
+        """Harvest every outstanding single-call iteration (call it before trusting the results of a run of
+        lazily checked iterations). Raises Overflow if one of them exceeded the capacity."""
+        err = None
+        for par in (self.parity, self.parity ^ 1):
+            if self.pending[par]:
+                try:
+                    self.harvest(par)
+                except Workspace.Overflow as ex:
+                    err = ex
+        if err is not None:
+            raise err
+        return self.last_Rs
 
     class Overflow(RuntimeError):
         pass
@@ -229,7 +264,8 @@ def same_view(cam_a, cam_b):
 
 
 def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur=False, return_pkg=False,
-                             dedupe_views=False, gray_event_views=True, gt_ready=None, accumulate=False, no_sync=True):
+                             dedupe_views=False, gray_event_views=True, gt_ready=None, accumulate=False, no_sync=True,
+                             lazy_check=False):
     """train.py:144-212 up to and including loss.backward(): sets .grad on pc's six leaves and on c,
     returns the loss (0-dim device tensor). With return_pkg also the first render's package
     (render, viewspace_points with .grad, visibility_filter, radii) that train.py:317-320 consumes.
@@ -253,6 +289,14 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     no_sync: after the first call (which reads num_rendered back like the reference and sizes a
     persistent Workspace from it) no forward blocks the host any more; see Workspace.
 
+    lazy_check: the host does not wait for this iteration's num_rendered at all; they are read (and compared
+    with the workspace capacity) two calls later, when their buffer set comes up for reuse, so the host runs up to
+    two iterations ahead of the GPU (at event-camera resolutions an iteration is shorter than its enqueue).
+    An iteration that exceeded the capacity is then REPORTED late -- Workspace.Overflow from a later call or from
+    Workspace.drain(), after the buffers were enlarged -- instead of being repeated; the capacity is kept 30 % above
+    the largest count seen and grown ahead of need, so this is an exceptional event. Default off: the iteration
+    waits for its own forwards (not for its backward) and repeats itself on overflow.
+
     accumulate: add this view-pair's gradients to the ones the previous call left (several pairs per
     optimizer step, e.g. BASELINE config c5 with 64 pairs per step); the returned loss is this
     pair's. The caller divides by the number of pairs (or lets parallel.allreduce_flat average over
@@ -266,7 +310,7 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
         ws = _workspace_for(pc, cam_train) if no_sync and pc._xyz.shape[0] > 0 else None
         if ws is not None:
             return _event_iteration_single_call(pc, (cam_train, cam_now, cam_next), gt, c, bg, deblur, return_pkg, 1, gt_ready,
-                                                accumulate, ws, shared=True)
+                                                accumulate, ws, shared=True, lazy=lazy_check)
         if accumulate:
             raise RuntimeError("accumulate=True with dedupe_views needs the workspace of a previous call")
         return _event_iteration_two_renders(pc, cam_train, cam_next, gt, c, bg, deblur, return_pkg, gt_ready, no_sync)
@@ -274,7 +318,7 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     ws = _workspace_for(pc, cam_train) if no_sync and pc._xyz.shape[0] > 0 else None
     if ws is not None:
         return _event_iteration_single_call(pc, (cam_train, cam_now, cam_next), gt, c, bg, deblur, return_pkg, ec, gt_ready,
-                                            accumulate, ws)
+                                            accumulate, ws, lazy=lazy_check)
     sts = [_forward_raw(pc, cam_train, bg, ws=ws, slot=0), _forward_raw(pc, cam_now, bg, channels=ec, ws=ws, slot=1),
            _forward_raw(pc, cam_next, bg, channels=ec, ws=ws, slot=2)]
     if ws is None and no_sync and pc._xyz.shape[0] > 0:
@@ -319,10 +363,17 @@ def event_iteration_backward(pc, cam_train, cam_now, cam_next, gt, c, bg, deblur
     return loss
 
 
-def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, gt_ready, accumulate, ws, shared=False):
-    """The whole iteration through ONE C call (e3_event_iteration) on the persistent workspace: no host
-    synchronisation, no per-render Python work. Falls back to itself once if the workspace overflowed."""
+def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, gt_ready, accumulate, ws, shared=False, lazy=False):
+    """The whole iteration through ONE C call (e3_event_iteration) on the persistent workspace: no per-render
+    Python work, and the only host wait is for the forwards' num_rendered (none at all with lazy=True, see
+    event_iteration_backward). Falls back to itself once if the workspace overflowed (lazy=False)."""
     L = _lib.lib()
+    if lazy:
+        if ws.pending[ws.parity]:
+            ws.harvest(ws.parity)          # the iteration before the previous one; its forwards finished long ago
+    else:
+        ws.drain()
+    par = ws.parity
     dev = pc._xyz.device
     P, D = pc._xyz.shape[0], int(pc.active_sh_degree)
     H, W = ws.H, ws.W
@@ -352,7 +403,7 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
     out = torch.empty(5, dtype=torch.float32, device=dev)
     d_mean2D = None if (accumulate and not shared) else torch.empty_like(pc._xyz)
     if shared:
-        ws.r_host[1].zero_()
+        ws.r_host2[par, 1].zero_()
     a = ws.args
     a.P, a.active_sh_degree, a.width, a.height = P, D, W, H
     a.binning_capacity, a.scale_modifier, a.accumulate = ws.cap, 1.0, int(bool(accumulate) or mc is not None)
@@ -374,19 +425,21 @@ def _event_iteration_single_call(pc, cams3, gt, c, bg, deblur, return_pkg, ec, g
             v.out_color, v.radii, v.seed = colors[k].data_ptr(), radii[k].data_ptr(), ws.seed(k, chans[k]).data_ptr()
         else:       # only the seed buffer of the skipped view is used: the total seed of the shared view
             v.out_color, v.radii, v.seed = None, None, ws.seed(k, 3).data_ptr()
-        v.num_rendered_host = ws.r_host[k].data_ptr()
+        v.num_rendered_host = ws.r_host2[par, k].data_ptr()
     a.gt_now, a.gt_next, a.gt_intensity = gt["event_now"].data_ptr(), gt["event_next"].data_ptr(), gt["intensity"].data_ptr()
     a.gt_blur = None if blur is None else blur.data_ptr()
     a.gt_is_u8, a.c, a.out5, a.loss_scratch = int(u8), c.data_ptr(), out.data_ptr(), ws.loss_scratch.data_ptr()
-    a.forwards_done_event = ws.fw_event.cuda_event
+    a.forwards_done_event = ws.fw_events[par].cuda_event
     stream = torch.cuda.current_stream(dev)
     a.wait_before_loss_event = gt_ready.cuda_event if gt_ready is not None else None
     with torch.cuda.device(dev):
         code = L.e3_event_iteration(ctypes.byref(a), stream.cuda_stream)
     _lib.check(code)
-    ws.pending_single = True
+    ws.pending[par] = True
+    ws.cap_used[par] = ws.cap
+    ws.parity = par ^ 1
     try:
-        Rs = ws.check()
+        Rs = (ws.last_Rs or [0, 0, 0]) if lazy else ws.harvest(par)
     except Workspace.Overflow:
         if mc is not None:
             raise RuntimeError("event_3dgs_b200.fused: workspace overflow during a step whose gradients were already reduced "

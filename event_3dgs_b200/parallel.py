@@ -52,6 +52,10 @@ def allreduce_flat(flat, world=None):
         flat.div_(world)
 
 
+class NoMulticast(RuntimeError):
+    """The symmetric-memory rendezvous worked but the system offers no NVLS multicast address."""
+
+
 class FusedGradientExchange:
     """Gradient exchange over NVLink 5 / NVSwitch with our own kernels instead of an NCCL call.
 
@@ -80,7 +84,7 @@ class FusedGradientExchange:
         self.hdl = symm.rendezvous(self.buf, group)
         mc = int(self.hdl.multicast_ptr)
         if mc == 0:
-            raise RuntimeError("FusedGradientExchange: no NVLS multicast support on this system")
+            raise NoMulticast("FusedGradientExchange: no NVLS multicast support on this system")
         self.delta = mc - self.buf.data_ptr()
         self.world, self.rank = int(self.hdl.world_size), int(self.hdl.rank)
         self.numel = numel
@@ -126,22 +130,33 @@ def fused_exchange_for(pc, numel, device, mode="pull"):
     pc._grad_exchange_cache = None
     try:
         ex = FusedGradientExchange(numel, device, mode=mode)
-    except Exception:
-        _EXCHANGE_UNAVAILABLE = True          # same outcome on every rank of a homogeneous box
+    except NoMulticast as e:
+        # the one expected reason (same outcome on every rank of a homogeneous box): said once, then NCCL is used.
+        # Anything else -- a failed rendezvous, an allocation error -- is a fault and propagates.
+        import warnings
+        warnings.warn("event_3dgs_b200.parallel: %s; gradients are exchanged with NCCL instead" % e)
+        _EXCHANGE_UNAVAILABLE = True
         return None
     pc._grad_exchange_cache = ex
     return ex
 
 
 def allreduce_densification_stats(grad_norm_increment, denom_increment, max_radii2D):
-    """In-place: SUM of the two accumulator increments, MAX of the screen radii."""
+    """In-place: SUM of the two accumulator increments, MAX of the screen radii -- as ONE collective over a
+    packed 12-byte-per-Gaussian buffer: every rank contributes its three rows [3, P] and receives all ranks'
+    (all-gather, 12 P bytes per rank), then sums / maximises locally. One launch instead of three reductions; the
+    rows are tiny against the gradient buffer, so the gathered volume does not matter."""
     if not dist.is_initialized() or dist.get_world_size() == 1:
         return
-    h = [dist.all_reduce(grad_norm_increment, op=dist.ReduceOp.SUM, async_op=True),
-         dist.all_reduce(denom_increment, op=dist.ReduceOp.SUM, async_op=True),
-         dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, async_op=True)]
-    for x in h:
-        x.wait()
+    world = dist.get_world_size()
+    P = max_radii2D.shape[0]
+    packed = torch.stack((grad_norm_increment.reshape(P), denom_increment.reshape(P), max_radii2D.reshape(P).to(grad_norm_increment.dtype)))
+    gathered = torch.empty(world * 3, P, dtype=packed.dtype, device=packed.device)
+    dist.all_gather_into_tensor(gathered, packed.contiguous())
+    gathered = gathered.view(world, 3, P)
+    grad_norm_increment.copy_(gathered[:, 0].sum(0).view_as(grad_norm_increment))
+    denom_increment.copy_(gathered[:, 1].sum(0).view_as(denom_increment))
+    max_radii2D.copy_(gathered[:, 2].max(0).values.view_as(max_radii2D).to(max_radii2D.dtype))
 
 
 def densification_increments(viewspace_grad, visibility_filter, radii):

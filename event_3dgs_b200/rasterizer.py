@@ -7,6 +7,7 @@ submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py
 torch is used for device memory, streams and autograd plumbing only.
 """
 import ctypes
+import threading
 import os
 from typing import NamedTuple
 
@@ -72,7 +73,26 @@ def verify_no_sync(block=True):
             _verify_slot(r, k, block)
 
 # ---- workspace callbacks (replace resizeFunctional, rasterize_points.cu:27-33) ----
-_slots = {}
+# The buffers handed out during ONE forward call, per host thread: the C call runs the callback synchronously on
+# the calling thread, so a thread-local dictionary is private to the call in flight (one thread per GPU).
+class _Slots(threading.local):
+    def __init__(self):
+        self.d = {}
+
+    def clear(self):
+        self.d = {}
+
+    def __setitem__(self, k, v):
+        self.d[k] = v
+
+    def __getitem__(self, k):
+        return self.d[k]
+
+    def get(self, k, default=None):
+        return self.d.get(k, default)
+
+
+_slots = _Slots()
 
 
 def _alloc(ctx, nbytes):

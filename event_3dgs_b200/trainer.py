@@ -80,7 +80,8 @@ class Trainer:
     otherwise one [3,H,W] frame."""
 
     def __init__(self, pc, cams_train, cams_event, gt_for, opt=None, event=True, gray=True, deblur=False, extent=1.0,
-                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True, dedupe_views=True):
+                 spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True, dedupe_views=True,
+                 lazy_check=True):
         self.pc, self.cams_train, self.cams_event, self.gt_for = pc, cams_train, cams_event, gt_for
         self.opt = opt or optimization_defaults()
         self.event, self.gray, self.deblur = event, gray, deblur
@@ -108,6 +109,15 @@ class Trainer:
         self.seed = seed
         self.iteration = 0
         self.rest_skipped = 0                    # Adam steps of f_rest that were pure no-ops (see _step_optimizers)
+        self.lazy_check = lazy_check             # fused.event_iteration_backward(lazy_check=...): host up to two steps ahead
+        if fused_exchange == "push" and world > 1 and self.opt.densify_until_iter > 0:
+            # multimem.red applies every rank's additions to each copy in arrival order: the copies of the gradient
+            # agree to rounding, not bit for bit, and replicas that densify on their own copy may then disagree on the
+            # new row count (and hang in the next collective). "pull" (one in-switch sum, broadcast) and NCCL give
+            # identical copies.
+            raise ValueError("fused_exchange='push' leaves the replicas' gradients equal only to fp32 rounding; it cannot be "
+                             "combined with densification (set opt.densify_until_iter = 0, or use 'pull')")
+        self.late_overflows = 0
         if event:
             self.opt.opacity_reset_interval = 10000          # train.py:126
         self.last = {}
@@ -130,7 +140,9 @@ class Trainer:
         # gradient exchange fused into the backward kernels (parallel.FusedGradientExchange) whenever the
         # no-sync workspace path is active on this model; otherwise local accumulation + one NCCL all-reduce
         exchange = None
-        if self.world >= 4 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[0]]) is not None:
+        # every rank decides from the camera IT renders first; the ranks agree because all cameras of a run have one
+        # image size (checked below after the backward: the gradients must have landed in the exchange buffer)
+        if self.world >= 4 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[self.my_pairs[0]]]) is not None:
             exchange = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), self.dev,
                                                    mode=self.fused_exchange if isinstance(self.fused_exchange, str) else "pull")
         pc._grad_exchange = exchange
@@ -138,9 +150,17 @@ class Trainer:
         for k, b in enumerate(self.my_pairs):
             index = indices[b]
             if self.event:
-                r = fused.event_iteration_backward(pc, self.cams_train[index], self.cams_event[index], self.cams_event[index + 1],
-                                                   self.gt_for(index), self.c, bg, deblur=self.deblur, return_pkg=(k == 0),
-                                                   accumulate=k > 0, dedupe_views=self.dedupe_views)
+                call = lambda: fused.event_iteration_backward(
+                    pc, self.cams_train[index], self.cams_event[index], self.cams_event[index + 1], self.gt_for(index), self.c, bg,
+                    deblur=self.deblur, return_pkg=(k == 0), accumulate=k > 0, dedupe_views=self.dedupe_views,
+                    lazy_check=self.lazy_check)
+                try:
+                    r = call()
+                except fused.Workspace.Overflow:
+                    # lazy_check: an iteration two steps back produced more instances than its buffers held (they
+                    # have been enlarged since); its image and gradients missed the excess. Counted, not repeated.
+                    self.late_overflows += 1
+                    r = call()
             else:
                 if k > 0:
                     raise RuntimeError("several pairs per rank and step are implemented for the event mode only")
@@ -151,6 +171,9 @@ class Trainer:
             else:
                 loss = r
             loss_sum = loss if loss_sum is None else loss_sum + loss
+        if exchange is not None and pc._grad_flat is not exchange.buf:
+            raise RuntimeError("event_3dgs_b200.trainer: the backward pass did not accumulate into the exchange buffer "
+                               "(a camera of another image size than the workspace?); the gradient exchange would reduce stale data")
         if exchange is not None and exchange.mode == "push":
             exchange.end()                      # barrier: every rank's reductions have landed in every copy
         elif exchange is not None:
@@ -182,6 +205,8 @@ class Trainer:
         return self.last["loss"]
 
     def _add_stats(self, pkg):
+        """Densification statistics of train.py:317-320 from the FIRST view pair of this rank's share of the step
+        (the reference has one pair per step); further pairs of a rank add gradients but no statistics."""
         grad, radii = pkg["viewspace_points"].grad, pkg["radii"]
         if self.world == 1:
             dn.add_densification_stats(self.state, grad, radii)

@@ -418,6 +418,9 @@ typedef struct e3_event_iteration_args {
 	                                cross-rank barrier, runs the iteration(s), passes a second barrier, and
 	                                then holds the sum over all ranks. */
 } e3_event_iteration_args;
+/* Not re-entrant per device: the two side streams and their fork/join events exist once per device, so one
+ * host thread per GPU may be inside this call at a time (the one-process-per-GPU model of SURVEY.md 8b). On any
+ * return, error returns included, `stream` is ordered behind all work the call gave to its side streams. */
 E3_API int e3_event_iteration(const e3_event_iteration_args* args_host, void* stream);
 
 /* Replaces CudaRasterizer::Rasterizer::markVisible (cuda_rasterizer/rasterizer.h:24-29,
@@ -428,7 +431,9 @@ E3_API int e3_mark_visible(int P, const float* means3D, const float* viewmatrix,
 /* Replaces simple_knn._C.distCUDA2 (call site scene/gaussian_model.py:134; implementation in the
  * un-vendored submodule submodules/simple-knn @ 9302c6d): mean_dist2[i] = mean of the squared
  * Euclidean distances from point i to its 3 nearest OTHER points (exact; coincident points count
- * with distance 0; fewer than 4 points leave FLT_MAX terms in the mean, as upstream does).
+ * with distance 0; fewer than 4 points leave FLT_MAX terms in the mean. That last rule is how the
+ * upstream kernel is REMEMBERED to behave (its best-distance slots start at FLT_MAX): the source is
+ * not in the reference tree and the reference holds no vector for it, so it is not evidence).
  * points is float[P,3]; scratch is caller-owned device memory of e3_dist2_scratch_bytes(P) bytes,
  * 256-byte aligned. */
 E3_API size_t e3_dist2_scratch_bytes(int P);

@@ -298,6 +298,39 @@ def test_no_sync_workspace_path_and_overflow_recovery(cuda_dev):
         assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
 
 
+def test_lazy_check_runs_ahead_and_reports_overflow_late(cuda_dev):
+    """lazy_check: num_rendered of an iteration is looked at two calls later (the host never waits for the
+    current one); results are those of the checked route, and an iteration that exceeded the workspace capacity
+    is reported by a later call or by Workspace.drain(), after the buffers have been enlarged."""
+    from event_3dgs_b200 import fused
+    pl, pc, cams, gt, bg, c = _setup(30_000, 346, 260, 0, False)
+    leaves = pc.leaves() + [c]
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg)          # sizes the workspace
+    la, pa = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True)
+    ga = [p.grad.clone() for p in leaves]
+    ws = pc._e3_ws
+    for k in range(4):
+        lb, pb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True, lazy_check=True)
+        assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
+        assert torch.equal(pb["render"], pa["render"])
+        for p, a in zip(leaves, ga):
+            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    assert ws.pending[0] and ws.pending[1]                 # two iterations are still unchecked
+    assert ws.drain() == pa["num_rendered"] and not any(ws.pending)
+    # overflow: nothing is raised by the call that overflows, nor by the next one ...
+    ws.resize(4096)
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, lazy_check=True)
+    fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, lazy_check=True)
+    with pytest.raises(fused.Workspace.Overflow):           # ... but by the one that reuses its buffer set
+        fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, lazy_check=True)
+    assert ws.cap >= max(pa["num_rendered"]) and ws.overflows >= 1
+    with pytest.raises(fused.Workspace.Overflow):
+        ws.drain()                                          # the second overflowed iteration
+    lc, pc_pkg = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True, lazy_check=True)
+    ws.drain()
+    assert torch.equal(pc_pkg["render"], pa["render"])
+
+
 def _fused_vs_dropin(pl, pc, cams, gt, bg, c, calls=2, tol=3e-4):
     """Both calls of the fused path (the workspace-sizing one and the no-sync single call) against autograd."""
     from event_3dgs_b200 import fused
@@ -396,3 +429,29 @@ def test_create_from_pcd_matches_reference_initialisation(cuda_dev):
         assert got.shape == d[name].shape, name
         assert np.abs(got - d[name]).max() <= tol, name
     assert pc.active_sh_degree == 0 and pc.max_sh_degree == 3
+
+
+def test_second_device_in_the_same_process(cuda_dev):
+    """One process driving two GPUs: the kernels that need more than 48 KB of dynamic shared memory (SH degree > 0)
+    get their launch attribute per device, so the second device works like the first (needs 2 visible GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    from event_3dgs_b200 import fused
+    from event_3dgs_b200 import pipeline as pl
+    from event_3dgs_b200 import synthetic as syn
+    sc = syn.make_scene(dict(P=5_000, W=128, H=96, sh_degree=2, deblur=False), seed=1)
+    losses = []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            pc = pl.GaussianParams(sc["gaussians"], dev)
+            cams = [pl.make_camera(c, dev) for c in sc["cameras"][:4]]
+            gt = {k: torch.as_tensor(v).to(dev) for k, v in sc["gt"].items()}
+            c = torch.nn.Parameter(torch.tensor(0.17, device=dev))
+            bg = torch.zeros(3, device=dev)
+            for _ in range(2):
+                loss = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
+            torch.cuda.synchronize(dev)
+            losses.append(float(loss))
+            assert torch.isfinite(pc._features_rest.grad).all() and pc._features_rest.grad.abs().max() > 0
+    assert abs(losses[0] - losses[1]) <= 1e-6 * abs(losses[0])

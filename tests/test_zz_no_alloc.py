@@ -42,9 +42,30 @@ def test_noalloc_scan_matches_regular_entry_point_twice_in_a_row(cuda_dev):
         out, tot, ref, ref_tot = _scan_both(L, _lib, a, cuda_dev)
         assert torch.equal(out, ref)
         assert torch.equal(tot, ref_tot)
+        # and the whole array against numpy, not only through the sibling entry point
         cs = np.cumsum(a.astype(np.uint64))
+        got = out.cpu().numpy().view(np.uint32)
+        assert got[0] == 0 and np.array_equal(got[1:], cs[:-1].astype(np.uint32))
         assert int(tot.item()) & 0xffffffff == int(cs[-1]) & 0xffffffff
-        assert int(out[-1].item()) & 0xffffffff == int(cs[-2]) & 0xffffffff
+
+
+def test_noalloc_scan_in_place(cuda_dev):
+    """in == out is allowed (every thread reads its values before it writes them): a caller without memory to
+    spare can scan its counts where they lie."""
+    from event_3dgs_b200 import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(7)
+    for n in (1, 2049, 1_000_003):
+        a = rng.integers(0, 50, n, dtype=np.uint32)
+        buf = torch.as_tensor(a.view(np.int32)).to(cuda_dev)
+        tot = torch.zeros(1, dtype=torch.int32, device=cuda_dev)
+        _lib.check(L.e3_exclusive_scan_noalloc(buf.data_ptr(), buf.data_ptr(), n, tot.data_ptr(),
+                                               torch.cuda.current_stream(cuda_dev).cuda_stream))
+        torch.cuda.synchronize(cuda_dev)
+        cs = np.cumsum(a.astype(np.uint64))
+        got = buf.cpu().numpy().view(np.uint32)
+        assert got[0] == 0 and np.array_equal(got[1:], cs[:-1].astype(np.uint32))
+        assert int(tot.item()) == int(cs[-1])
 
 
 def test_noalloc_scan_rejects_oversize_and_handles_empty(cuda_dev):
