@@ -99,6 +99,8 @@ SIGNATURES["e3_rasterize_forward_ws"] = (_i, [_vp, _vp, _sz, _vp, _vp, _i, _i, _
 SIGNATURES["e3_rasterize_backward_raw_dual"] = (_i, [_i, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _f, _f,
                                                     _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp])
 SIGNATURES["e3_multimem_add"] = (_i, [_vp, _vp, _sz, _f, _vp])
+SIGNATURES["e3_nvls_sharded_adam"] = (_i, [ctypes.POINTER(AdamGroup), _i, _i, ctypes.c_double, ctypes.c_double, ctypes.c_longlong,
+                                          ctypes.c_longlong, _i, _i, _f, _vp])
 SIGNATURES["e3_nvls_allreduce"] = (_i, [_vp, _sz, _i, _i, _f, _vp])
 SIGNATURES["e3_densification_stats"] = (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp])
 SIGNATURES["e3_densify_scratch_bytes"] = (_sz, [_i])

@@ -114,6 +114,142 @@ class FusedGradientExchange:
         self.hdl.barrier(channel=0)
 
 
+def shard_range(n, rank, world):
+    """Floats [lo, hi) of an n-float parameter group that `rank` owns in e3_nvls_sharded_adam: the rank-th share of
+    its 16-byte vectors, ceil(vectors / world) each (the last ranks may own less, or nothing)."""
+    nv = (n + 3) // 4
+    per = (nv + world - 1) // world
+    b = min(per * rank, nv)
+    e = min(b + per, nv)
+    return min(4 * b, n), min(4 * e, n)
+
+
+class ShardedAdam:
+    """Gradient exchange and optimizer step of the replicated trainer as ONE kernel per rank (e3_nvls_sharded_adam):
+    in-switch sum of the rank's 1/world of the gradient vectors -> Adam on those rows -> multicast store of the new
+    parameters into every rank's copy ("reduce-scatter -> sharded Adam -> all-gather"). The model's
+    six leaf tensors and the event threshold c are re-homed as views into one symmetric-memory buffer (adopt(),
+    collective); the gradients already live in the symmetric buffer of FusedGradientExchange. Optimizer state keeps
+    torch's layout (full-size exp_avg / exp_avg_sq per parameter), but a rank only advances the rows it owns: call
+    sync_moments() before anything that reads or edits whole moment tensors (densification, opacity reset, a
+    replicated optimizer step, checkpoints)."""
+
+    LEAVES = (("xyz", "_xyz"), ("features_dc", "_features_dc"), ("opacity", "_opacity"), ("scaling", "_scaling"),
+              ("rotation", "_rotation"), ("features_rest", "_features_rest"))
+
+    def __init__(self, device, group=None):
+        self.device, self.group = device, group or dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.pbuf = self.hdl = None
+        self.delta = 0
+        self.moments_full = True
+
+    @staticmethod
+    def _rekey(optimizer, old, new):
+        for g in optimizer.param_groups:
+            for k, q in enumerate(g["params"]):
+                if q is old:
+                    g["params"][k] = new
+        if old in optimizer.state:
+            optimizer.state[new] = optimizer.state.pop(old)
+
+    def adopt(self, pc, c, optimizer, optimizer_c):
+        """Collective: moves the current parameter values into a fresh symmetric buffer and replaces the model's leaf
+        tensors (and c) by views into it; the optimizers' groups and states follow the new tensors. Returns c."""
+        import torch.distributed._symmetric_memory as symm
+        params = [getattr(pc, attr) for _, attr in self.LEAVES]
+        sizes = [(t.numel() + 3) // 4 * 4 for t in params] + [4]
+        self.pbuf = symm.empty(sum(sizes), dtype=torch.float32, device=self.device)
+        self.pbuf.zero_()
+        self.hdl = symm.rendezvous(self.pbuf, self.group)
+        mc = int(self.hdl.multicast_ptr)
+        if mc == 0:
+            raise NoMulticast("ShardedAdam: no NVLS multicast support on this system")
+        self.delta = mc - self.pbuf.data_ptr()
+        off = 0
+        with torch.no_grad():
+            for (name, attr), t, sz in zip(self.LEAVES, params, sizes[:-1]):
+                view = self.pbuf[off:off + t.numel()].view(t.shape)
+                view.copy_(t.detach())
+                new = torch.nn.Parameter(view)
+                self._rekey(optimizer, t, new)
+                setattr(pc, attr, new)
+                off += sz
+            cview = self.pbuf[off:off + 1].view(c.shape)
+            cview.copy_(c.detach())
+            cnew = torch.nn.Parameter(cview)
+            self._rekey(optimizer_c, c, cnew)
+        self.hdl.barrier(channel=0)          # every copy holds the parameters before anyone's multicast store can land
+        return cnew
+
+    def owns(self, pc):
+        return self.pbuf is not None and pc._xyz.data_ptr() == self.pbuf.data_ptr()
+
+    def _items(self, pc, c, optimizer, optimizer_c, D):
+        out = []
+        for name, attr in self.LEAVES:
+            if name == "features_rest" and D == 0:
+                continue
+            p = getattr(pc, attr)
+            grp = next(g for g in optimizer.param_groups if any(q is p for q in g["params"]))
+            out.append((p, pc._grad_views[name], optimizer, grp))
+        out.append((c, pc._grad_views["c"], optimizer_c, optimizer_c.param_groups[0]))
+        return out
+
+    @torch.no_grad()
+    def step(self, pc, c, optimizer, optimizer_c, exchange, grad_scale, D):
+        """One fused exchange + Adam step. `exchange` is the FusedGradientExchange whose buffer the backward pass
+        accumulated into (pc._grad_views are views of it); grad_scale turns the sum over ranks into the mean."""
+        from . import _lib
+        if pc._grad_flat is not exchange.buf:
+            raise RuntimeError("ShardedAdam.step: the gradients are not in the exchange buffer")
+        buckets = {}
+        for p, g, opt, grp in self._items(pc, c, optimizer, optimizer_c, D):
+            st = opt.state[p]
+            if len(st) == 0:
+                st["step"] = 0
+                st["exp_avg"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+                st["exp_avg_sq"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+            st["step"] = int(st["step"]) + 1
+            st.pop("_moments_zero", None)
+            b1, b2 = grp["betas"]
+            buckets.setdefault((st["step"], float(b1), float(b2)), []).append((p, g, st, float(grp["lr"]), float(grp["eps"])))
+        L = _lib.lib()
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        exchange.hdl.barrier(channel=0)          # every rank's local gradients are complete
+        for (t, b1, b2), items in buckets.items():
+            arr = (_lib.AdamGroup * len(items))()
+            for k, (p, g, st, lr, eps) in enumerate(items):
+                arr[k].param, arr[k].grad = p.data_ptr(), g.data_ptr()
+                arr[k].exp_avg, arr[k].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+                arr[k].n, arr[k].lr, arr[k].eps = p.numel(), lr, eps
+            with torch.cuda.device(self.device):
+                _lib.check(L.e3_nvls_sharded_adam(arr, len(items), t, b1, b2, exchange.delta, self.delta, self.rank, self.world,
+                                                  float(grad_scale), stream))
+        self.hdl.barrier(channel=0)              # every rank's parameter stores have landed everywhere
+        self.moments_full = False
+
+    @torch.no_grad()
+    def sync_moments(self, optimizers):
+        """Every rank receives, for every parameter, the moment rows their owners advanced (one broadcast per owner
+        and tensor; rare: before densification, opacity reset, checkpoints, or a replicated step)."""
+        if self.moments_full:
+            return
+        for opt in optimizers:
+            for grp in opt.param_groups:
+                for p in grp["params"]:
+                    st = opt.state.get(p, None)
+                    if not st or "exp_avg" not in st:
+                        continue
+                    for key in ("exp_avg", "exp_avg_sq"):
+                        flat = st[key].view(-1)
+                        for r in range(self.world):
+                            lo, hi = shard_range(flat.numel(), r, self.world)
+                            if hi > lo:
+                                dist.broadcast(flat[lo:hi], src=dist.get_global_rank(self.group, r), group=self.group)
+        self.moments_full = True
+
+
 _EXCHANGE_UNAVAILABLE = False
 
 

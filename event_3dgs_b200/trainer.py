@@ -81,7 +81,7 @@ class Trainer:
 
     def __init__(self, pc, cams_train, cams_event, gt_for, opt=None, event=True, gray=True, deblur=False, extent=1.0,
                  spatial_lr_scale=None, white_background=False, pairs_per_step=1, seed=0, rank=0, world=1, fused_exchange=True, dedupe_views=True,
-                 lazy_check=True):
+                 lazy_check=True, sharded_optimizer=False):
         self.pc, self.cams_train, self.cams_event, self.gt_for = pc, cams_train, cams_event, gt_for
         self.opt = opt or optimization_defaults()
         self.event, self.gray, self.deblur = event, gray, deblur
@@ -109,6 +109,11 @@ class Trainer:
         self.seed = seed
         self.iteration = 0
         self.rest_skipped = 0                    # Adam steps of f_rest that were pure no-ops (see _step_optimizers)
+        # world > 1: gradient exchange and Adam as one kernel per rank (parallel.ShardedAdam) on the iterations that
+        # neither densify nor reset the opacity; the others take the replicated route on synchronised moments
+        self.sharded_optimizer = bool(sharded_optimizer) and world > 1 and event
+        self.sharded = None
+        self.sharded_steps = 0
         self.lazy_check = lazy_check             # fused.event_iteration_backward(lazy_check=...): host up to two steps ahead
         if fused_exchange == "push" and world > 1 and self.opt.densify_until_iter > 0:
             # multimem.red applies every rank's additions to each copy in arrival order: the copies of the gradient
@@ -133,6 +138,19 @@ class Trainer:
                                    0, opt.position_lr_delay_mult, opt.position_lr_max_steps)
         if it % 1000 == 0 and pc.active_sh_degree < pc.max_sh_degree:
             pc.active_sh_degree += 1
+        densify_now = it < opt.densify_until_iter and it > opt.densify_from_iter and it % opt.densification_interval == 0
+        reset_now = it < opt.densify_until_iter and (it % opt.opacity_reset_interval == 0 or (self.white_background and it == opt.densify_from_iter))
+        if self.sharded_optimizer:
+            try:
+                if self.sharded is None:
+                    self.sharded = parallel.ShardedAdam(self.dev)
+                if not self.sharded.owns(pc):        # first step, and after every densification (collective)
+                    self.sharded.sync_moments([self.optimizer, self.optimizer_c])
+                    self.c = self.sharded.adopt(pc, self.c, self.optimizer, self.optimizer_c)
+            except parallel.NoMulticast as e:
+                import warnings
+                warnings.warn("event_3dgs_b200.trainer: %s; replicated optimizer instead" % e)
+                self.sharded_optimizer, self.sharded = False, None
         n_views = len(self.cams_train)
         indices = [pick_index(self.rng, n_views, self.event) for _ in range(self.pairs_per_step)]
         bg = torch.rand(3, device=self.dev) if opt.random_background else self.bg
@@ -142,7 +160,7 @@ class Trainer:
         exchange = None
         # every rank decides from the camera IT renders first; the ranks agree because all cameras of a run have one
         # image size (checked below after the backward: the gradients must have landed in the exchange buffer)
-        if self.world >= 4 and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[self.my_pairs[0]]]) is not None:
+        if self.world >= (2 if self.sharded_optimizer else 4) and self.event and self.fused_exchange and fused._workspace_for(pc, self.cams_train[indices[self.my_pairs[0]]]) is not None:
             exchange = parallel.fused_exchange_for(pc, fused.grad_flat_numel(pc, int(pc.active_sh_degree)), self.dev,
                                                    mode=self.fused_exchange if isinstance(self.fused_exchange, str) else "pull")
         pc._grad_exchange = exchange
@@ -174,7 +192,11 @@ class Trainer:
         if exchange is not None and pc._grad_flat is not exchange.buf:
             raise RuntimeError("event_3dgs_b200.trainer: the backward pass did not accumulate into the exchange buffer "
                                "(a camera of another image size than the workspace?); the gradient exchange would reduce stale data")
-        if exchange is not None and exchange.mode == "push":
+        use_sharded = (self.sharded_optimizer and exchange is not None and exchange.mode == "pull" and not densify_now and not reset_now
+                       and it < opt.iterations)
+        if use_sharded:
+            pass                                # exchange and Adam happen together below (ShardedAdam.step)
+        elif exchange is not None and exchange.mode == "push":
             exchange.end()                      # barrier: every rank's reductions have landed in every copy
         elif exchange is not None:
             exchange.allreduce(1.0 / self.pairs_per_step)     # one in-switch all-reduce kernel, mean over all pairs
@@ -183,7 +205,9 @@ class Trainer:
                 pc._grad_flat.div_(len(self.my_pairs))
             if self.world > 1:
                 parallel.allreduce_flat(pc._grad_flat, self.world)
-        self.last_exchange = ("nvls " + exchange.mode) if exchange is not None else ("nccl all-reduce" if self.world > 1 else "none")
+        self.last_exchange = "nvls sharded adam" if use_sharded else (("nvls " + exchange.mode) if exchange is not None else ("nccl all-reduce" if self.world > 1 else "none"))
+        if self.sharded is not None and not use_sharded:
+            self.sharded.sync_moments([self.optimizer, self.optimizer_c])       # a replicated step / state surgery follows
         self.last = {"loss": loss_sum / len(self.my_pairs), "indices": indices, "num_rendered": pkg0["num_rendered"]}
 
         if it < opt.densify_until_iter:                        # train.py:317-327
@@ -198,7 +222,15 @@ class Trainer:
             if it % opt.opacity_reset_interval == 0 or (self.white_background and it == opt.densify_from_iter):
                 dn.reset_opacity(pc, self.optimizer)
                 pc._opacity.grad = None        # replace_tensor_to_optimizer: the new opacity tensor has no grad
-        if it < opt.iterations:
+        if use_sharded:
+            D = int(pc.active_sh_degree)
+            rest = pc._features_rest
+            if D == 0 and self.optimizer.moments_are_zero(rest):
+                self.optimizer.advance_without_update(rest)         # as in _step_optimizers
+                self.rest_skipped += 1
+            self.sharded.step(pc, self.c, self.optimizer, self.optimizer_c, exchange, 1.0 / self.pairs_per_step, D)
+            self.sharded_steps += 1
+        elif it < opt.iterations:
             self._step_optimizers()
         self.optimizer.zero_grad(set_to_none=True)
         self.optimizer_c.zero_grad(set_to_none=True)

@@ -273,6 +273,18 @@ typedef struct e3_adam_group {
 E3_API int e3_adam_step(const e3_adam_group* groups_host, int num_groups, int step, double beta1,
 	double beta2, void* stream);
 
+/* Sharded Adam fused with the gradient exchange of the replicated multi-GPU trainer (SURVEY.md 8e upgrade path;
+ * no counterpart in the single-GPU reference, whose optimizer step is scene/gaussian_model.py:149-175 +
+ * train.py:330-332). Groups as for e3_adam_step, but `param` and `grad` point into buffers that exist in symmetric
+ * memory on all `world` ranks, with the byte offsets from them to their NVLS multicast aliases given; both are laid
+ * out in segments padded to 16 bytes, the moments are ordinary local arrays of n floats. Rank r owns the r-th
+ * 1/world of every group's 16-byte vectors: it fetches grad_scale * (sum over ranks of the gradient) from the switch
+ * (multimem.ld_reduce), applies Adam to those rows and its rows of the moments, and writes the new parameters into
+ * every rank's copy (multimem.st). One kernel. The caller places a cross-rank barrier on the stream before (all local
+ * gradients complete) and after (all parameters written). Moments of rows a rank does not own are not touched. */
+E3_API int e3_nvls_sharded_adam(const e3_adam_group* groups_host, int num_groups, int step, double beta1, double beta2,
+	long long grad_multicast_delta, long long param_multicast_delta, int rank, int world, float grad_scale, void* stream);
+
 /* Densification statistics of one iteration (train.py:317-320, scene/gaussian_model.py:405-407),
  * one launch: for every Gaussian with radii > 0 (the visibility filter of the first render)
  *   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |d_mean2D[:, :2]|; denom += 1.

@@ -42,9 +42,20 @@ def _worker(rank, world, port, out):
     gn, den, rad = parallel.densification_increments(vgrad, vis, radii)
     local = (gn.clone(), den.clone(), rad.clone())
     parallel.allreduce_densification_stats(gn, den, rad)
+    # moments of a sharded optimizer: every rank advanced only the rows it owns; sync_moments makes them whole
+    sh = parallel.ShardedAdam(torch.device("cpu"))
+    q = torch.nn.Parameter(torch.zeros(1001, 3))
+    opt = torch.optim.Adam([q], lr=0.1)
+    opt.state[q] = {"step": 3, "exp_avg": torch.full((1001, 3), -1.0), "exp_avg_sq": torch.full((1001, 3), -1.0)}
+    lo, hi = parallel.shard_range(q.numel(), rank, world)
+    opt.state[q]["exp_avg"].view(-1)[lo:hi] = torch.arange(lo, hi, dtype=torch.float32)
+    opt.state[q]["exp_avg_sq"].view(-1)[lo:hi] = 2.0 * torch.arange(lo, hi, dtype=torch.float32)
+    sh.moments_full = False
+    sh.sync_moments([opt])
+    moments = (opt.state[q]["exp_avg"].clone(), opt.state[q]["exp_avg_sq"].clone())
     flat = torch.arange(10, dtype=torch.float32) * (rank + 1)
     parallel.allreduce_flat(flat, world)
-    torch.save(dict(flat=flat, pairs=pairs, grads=[p.grad for p in params], stats=(gn, den, rad), local=local), out % rank)
+    torch.save(dict(flat=flat, pairs=pairs, moments=moments, grads=[p.grad for p in params], stats=(gn, den, rad), local=local), out % rank)
     dist.destroy_process_group()
 
 
@@ -61,6 +72,24 @@ def test_two_rank_gradient_and_stats_reduction(tmp_path):
         assert torch.allclose(g0, torch.full_like(g0, 3.5))
     for k in range(3):
         assert torch.equal(r[0]["stats"][k], r[1]["stats"][k])
+    for k in range(world):
+        assert torch.equal(r[k]["moments"][0].view(-1), torch.arange(3003, dtype=torch.float32))
+        assert torch.equal(r[k]["moments"][1].view(-1), 2.0 * torch.arange(3003, dtype=torch.float32))
     assert torch.allclose(r[0]["stats"][0], r[0]["local"][0] + r[1]["local"][0])
     assert torch.allclose(r[0]["stats"][1], r[0]["local"][1] + r[1]["local"][1])
     assert torch.equal(r[0]["stats"][2], torch.maximum(r[0]["local"][2], r[1]["local"][2]))
+
+
+def test_shard_range_partitions_every_group():
+    """parallel.shard_range = the row ranges e3_nvls_sharded_adam gives the ranks: disjoint, ordered, covering."""
+    sys.path.insert(0, ROOT)
+    from event_3dgs_b200.parallel import shard_range
+    for n in (1, 3, 4, 5, 1000, 1001, 3_000_003):
+        for w in (1, 2, 3, 8):
+            cover = 0
+            for k in range(w):
+                lo, hi = shard_range(n, k, w)
+                assert lo == cover or lo == hi == n, (n, w, k)
+                assert lo % 4 == 0 or lo == n
+                cover = max(cover, hi)
+            assert cover == n
