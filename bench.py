@@ -577,6 +577,23 @@ def main():
         del trn3
         del trn, pc_t
 
+    if use_fused and world > 1:
+        # extra: the whole training step on all ranks (one view-pair per rank and step): iteration + densification
+        # statistics + gradient exchange + Adam, (a) replicated optimizer behind the all-reduce, (b) exchange and Adam as one
+        # kernel per rank (e3_nvls_sharded_adam: in-switch sum of 1/world of the rows -> Adam -> multicast store)
+        from event_3dgs_b200 import trainer as tr
+        res = {}
+        for tag, sharded in (("replicated_adam", False), ("sharded_adam", True)):
+            pc_t = pl.GaussianParams(scene["gaussians"], dev)
+            trn = tr.Trainer(pc_t, cams, cams, lambda i: gt_dev, opt=tr.optimization_defaults(densify_from_iter=10 ** 9), event=True, deblur=deblur,
+                             extent=2.6, pairs_per_step=world, rank=rank, world=world, dedupe_views=False, sharded_optimizer=sharded)
+            for s in range(4):
+                trn.step()
+            ms_t, _, _ = timed(lambda s: trn.step(), args.steps)
+            res[tag] = {"value": world * 1e3 / (ms_t / args.steps), "unit": UNIT, "ms_per_step": ms_t / args.steps, "exchange": trn.last_exchange}
+            del trn, pc_t
+        line["train_loop"] = dict(res, what="three renders per pair, one pair per rank and step, statistics + exchange + Adam on every rank")
+
     if use_fused and world == 1:
         # extra: the non-event branch of train.py (one render, L1 + SSIM on the luma, :213-223) through
         # fused.frame_iteration_backward (fused SSIM kernel, no-sync workspace)
