@@ -75,12 +75,16 @@ GRAD_TOL_ATOMIC_CHAIN = 3e-4
 CHAIN_ARRAYS = ("dL_dmeans3D", "dL_dscales", "dL_drotations", "xyz", "scaling", "rotation")
 
 
-GRAD_TOL_ATOMIC_CHAIN_C5 = 1e-3      # 3M Gaussians at 1920x1080: see the measured spreads in BASELINE.md section 5
+# 3M Gaussians at 1920x1080: the reference build repeats ITSELF only to 6.5e-4 (dL_drotations) / 1.2e-4 (dL_dscales)
+# from one run to the next there (profiles/r2_parity_observed.json, ref_vs_ref/c5): a handful of ill-conditioned rows
+# out of 3M set the maximum. Two such runs against each other are held to ~4x that spread, and to GRAD_TOL on all
+# but 1e-4 of the rows (row-wise check in tests/test_timed_sizes_gpu.py).
+GRAD_TOL_ATOMIC_CHAIN_C5 = {"dL_drotations": 3e-3, "dL_dscales": 1e-3, "dL_dmeans3D": 3e-4}
 
 
 def grad_tol(name, two_atomic_runs=False, size=None):
     if two_atomic_runs and name in CHAIN_ARRAYS:
-        return GRAD_TOL_ATOMIC_CHAIN_C5 if size == "c5" else GRAD_TOL_ATOMIC_CHAIN
+        return GRAD_TOL_ATOMIC_CHAIN_C5.get(name, GRAD_TOL_ATOMIC_CHAIN) if size == "c5" else GRAD_TOL_ATOMIC_CHAIN
     return GRAD_TOL
 
 

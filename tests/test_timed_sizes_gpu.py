@@ -64,6 +64,10 @@ def test_dropin_bit_exact_vs_reference_cuda_at_timed_sizes(gc, name, P, W, H, ki
         observe("ours_vs_ours/%s/%s" % (name, k), rel_err(_np(g2[k]), a, fl[k]))
         e = observe("dropin_vs_ref/%s/%s" % (name, k), rel_err(a, b, fl[k]))
         assert e < grad_tol(k, two_atomic_runs=True, size=name), (k, e)
+        # row-wise: whatever the maximum over millions of rows does, (almost) every row agrees within GRAD_TOL of the scale
+        scale = max(float(np.abs(b).max()), fl[k], 1e-30)
+        rows_off = float((np.abs(a - b).reshape(a.shape[0], -1).max(axis=1) >= GRAD_TOL * scale).mean())
+        assert observe("dropin_vs_ref_rows_off/%s/%s" % (name, k), rows_off) <= 1e-4, (k, rows_off)
     culled = ~(fw["radii"] > 0)
     for k in KEYS:
         assert (g[k][culled] == 0).all()
