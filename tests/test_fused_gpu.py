@@ -125,6 +125,26 @@ def test_dist2_matches_bruteforce_oracle(cuda_dev):
         ref = ro.dist2(pts)
         assert np.array_equal(np.isinf(got), np.isinf(ref)) and (got[~np.isinf(got)] > 1e30).all()
     assert distCUDA2(torch.zeros(0, 3, device=cuda_dev)).shape == (0,)
+    # a COLMAP-like cloud: 1 % of far outliers at 100x the extent. The grid follows the bulk (robust extent), so the
+    # result is still exact and the running time stays that of a uniform cloud (a bounding-box grid would put
+    # nearly all points into a handful of cells and scan them serially: seconds).
+    import time
+    for n in (12_000, 300_000):
+        pts = rng.uniform(-1.0, 1.0, (n, 3)).astype(np.float32)
+        far = rng.choice(n, n // 100, replace=False)
+        pts[far] = rng.uniform(-100.0, 100.0, (far.size, 3)).astype(np.float32)
+        t = torch.as_tensor(pts).to(cuda_dev)
+        distCUDA2(t)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        got = distCUDA2(t).cpu().numpy()
+        dt = time.perf_counter() - t0
+        assert dt < 0.25, (n, dt)
+        idx = np.concatenate([rng.choice(n, 150, replace=False), far[:50]])
+        D = ((pts[idx, None, :].astype(np.float64) - pts[None, :, :]) ** 2).sum(-1)
+        D[np.arange(idx.size), idx] = np.inf
+        ref = np.sort(np.partition(D, 3, axis=1)[:, :3], 1).mean(1)
+        assert np.allclose(got[idx], ref, rtol=1e-4), n
     # 1M points (the size of a large COLMAP cloud): every value is finite, positive and consistent
     # with a brute-force check on a sample
     pts = rng.uniform(-1.3, 1.3, (1_000_000, 3)).astype(np.float32)
