@@ -142,7 +142,10 @@ __global__ void __launch_bounds__(256) radix_hist_all_kernel(const uint32_t* __r
 	}
 }
 
-__global__ void __launch_bounds__(E3_SORT_THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
+#ifndef E3_SORT_MIN_BLOCKS
+#define E3_SORT_MIN_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(E3_SORT_THREADS, E3_SORT_MIN_BLOCKS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
 	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
 	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist, volatile uint32_t* lookback,
 	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev)
