@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import torch
 
-from tests.common import rel_err
+from tests.common import GRAD_TOL, grad_tol, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -48,8 +48,9 @@ def test_fused_iteration_matches_dropin_autograd(cuda_dev, sh_degree, deblur):
         if n == "features_rest" and sh_degree == 0:
             assert (a == 0).all() and (b == 0).all()
             continue
-        assert rel_err(b.cpu().numpy(), a.cpu().numpy(), fl) < 2e-4, n
-    assert rel_err(pkg_b["viewspace_points"].grad.cpu().numpy(), vs_a.cpu().numpy()) < 2e-4
+        assert rel_err(b.cpu().numpy(), a.cpu().numpy(), fl) < grad_tol(n, two_atomic_runs=True), n
+    same = (pkg_a["radii"] == pkg_b["radii"]).cpu().numpy()
+    assert rel_err(pkg_b["viewspace_points"].grad.cpu().numpy()[same], vs_a.cpu().numpy()[same]) < 2 * GRAD_TOL
     assert torch.equal(pkg_b["visibility_filter"], pkg_b["radii"] > 0)
 
 
@@ -268,8 +269,8 @@ def test_frame_iteration_matches_dropin_autograd(cuda_dev):
         assert abs(la.item() - lb.item()) <= 1e-5 * abs(la.item())
         # two fp32 pipelines whose activations / SH colours round differently (ATen vs in-kernel): a
         # borderline alpha >= 1/255 or radius decision may flip for single Gaussians
-        for a, b in zip(ga, gb):
-            assert rel_err(b.cpu().numpy(), a.cpu().numpy()) < 5e-4
+        for n, a, b in zip(("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity"), ga, gb):
+            assert rel_err(b.cpu().numpy(), a.cpu().numpy()) < grad_tol(n, two_atomic_runs=True), (gray, n)
 
 
 def test_accumulate_over_view_pairs(cuda_dev):
@@ -351,7 +352,7 @@ def test_lazy_check_runs_ahead_and_reports_overflow_late(cuda_dev):
     assert torch.equal(pc_pkg["render"], pa["render"])
 
 
-def _fused_vs_dropin(pl, pc, cams, gt, bg, c, calls=2, tol=3e-4):
+def _fused_vs_dropin(pl, pc, cams, gt, bg, c, calls=2):
     """Both calls of the fused path (the workspace-sizing one and the no-sync single call) against autograd."""
     from event_3dgs_b200 import fused
     leaves = pc.leaves() + [c]
@@ -365,8 +366,8 @@ def _fused_vs_dropin(pl, pc, cams, gt, bg, c, calls=2, tol=3e-4):
             p.grad = None
         lb = fused.event_iteration_backward(pc, cams[1], cams[1], cams[2], gt, c, bg)
         assert abs(la.item() - lb.item()) <= 1e-5 * max(abs(la.item()), 1e-6), k
-        for a, p in zip(ga, leaves):
-            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-12) < tol, k
+        for n, a, p in zip(("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity", "c"), ga, leaves):
+            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-12) < grad_tol(n, two_atomic_runs=True), (k, n)
 
 
 def test_fused_edge_cases(cuda_dev):

@@ -8,12 +8,14 @@ import numpy as np
 import pytest
 import torch
 
-from tests.common import oracle_forward, rel_err, scene_inputs, smooth_dL
+from tests.common import grad_tol, observe, oracle_forward, rel_err, scaled_err, scene_inputs, smooth_dL
 
 pytestmark = pytest.mark.gpu
 
 IMG_TOL = 1e-5
 GRAD_TOL = 1e-4
+SCALED_TOL = 5e-3       # max |a - b| / (|b| + 0.01 max|b|) against the fp64-accumulating oracle, arrays behind the conic ->
+                        # covariance chain; the others are held to GRAD_TOL on this metric too
 
 CASES = [
     # P, W, H, seed, kind, bg
@@ -97,6 +99,11 @@ def test_backward_vs_reference_cuda_and_oracle(gc, P, W, H, seed, kind, bg):
     fl["dL_drotations"] = 1e-3 * float(np.abs(go["dL_dscales"]).max()) * float(np.abs(inp["scales"]).max())
     for k in keys:
         assert rel_err(_np(g[k]).reshape(go[k].shape), go[k], fl[k]) < GRAD_TOL, ("oracle", k)
+        # scale-aware companion (tests/common.scaled_err): an element is held against |itself| + 1 % of the array maximum,
+        # so rows two orders of magnitude below the maximum are checked too, not only the largest ones
+        if not (k == "dL_drotations" and kind == "init"):
+            e = observe("scaled_vs_oracle/%dx%d_%s/%s" % (W, H, kind, k), scaled_err(_np(g[k]).reshape(go[k].shape), go[k], 1e-2))
+            assert e < (SCALED_TOL if k in ("dL_dmeans3D", "dL_dscales", "dL_drotations") else GRAD_TOL), ("oracle, scale-aware", k, e)
     if ref_cuda.available():
         ref, R, out, radii = gc.ref_forward(inp)
         gr = ref.backward(gc.T(dL))
@@ -333,7 +340,7 @@ def test_randomised_scenes_bit_exact_vs_reference_cuda(gc, seed):
     for k2 in ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dscales", "dL_drotations"]:
         a, b = _np(g[k2]), _np(gr[k2]).reshape(_np(g[k2]).shape)
         assert np.isfinite(a).all(), k2
-        assert rel_err(a, b) < 2e-4, k2       # two unordered fp32 summations against each other
+        assert rel_err(a, b) < grad_tol(k2, two_atomic_runs=True), k2       # two unordered fp32 summations against each other
 
 
 def test_full_size_c5_properties(gc):
