@@ -303,6 +303,7 @@ def main():
         return 2 + (7 * (step * pairs + b)) % 80
 
     exchange_used = {"kind": "none" if world == 1 else "nccl all-reduce (AVG) of the flat gradient buffer"}
+    overflowed = []          # steps whose instance count exceeded the workspace (lazy check): reported in the line
 
     def iteration(step, gt, sync_grads=True, gt_ready=None):
         for p in leaves:
@@ -320,8 +321,13 @@ def main():
             if use_fused:
                 # lazy_check: num_rendered of a step is read (and checked against the workspace capacity) two steps
                 # later; drain_workspace() below verifies that no timed step had exceeded it
-                l = fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur,
-                                                   gt_ready=gt_ready if k == 0 else None, accumulate=k > 0, lazy_check=True)
+                call = lambda: fused.event_iteration_backward(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur,
+                                                              gt_ready=gt_ready if k == 0 else None, accumulate=k > 0, lazy_check=True)
+                try:
+                    l = call()
+                except fused.Workspace.Overflow as ex:      # reported two steps late; the buffers have been enlarged
+                    overflowed.append(str(ex))
+                    l = call()
             else:
                 l, pkg = pl.event_iteration(pc, cams[v], cams[v], cams[v + 1], gt, c_param, bg, deblur=deblur)
                 l.backward()              # autograd accumulates into .grad over the pairs
@@ -402,8 +408,6 @@ def main():
     clk = clocks.stop(w0, w1) if clocks else None
     ms_per_step = ms / args.steps
     value = pairs * 1e3 / ms_per_step
-
-    overflowed = []
 
     def drain_workspace():
         # a step that produced more instances than the workspace held dropped the excess: say so in the line
