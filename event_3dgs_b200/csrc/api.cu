@@ -216,7 +216,8 @@ static int forward_impl(
 	E3_STAGE(E3_STAGE_TILE_RANGES, e3_launch_tile_order(im.ranges, (int)T, im.tile_order, st));
 	// single-channel raw mode blends against the luma of the background (written by the preprocess kernel)
 	const float* bg_used = (raw && channels == 1) ? reinterpret_cast<const float*>(g.flags) + 2 : background;
-	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib, out_color, st));
+	E3_STAGE(E3_STAGE_RENDER_FWD, e3_launch_render_forward(f, im.ranges, im.tile_order, b.val[0], g.rec, bg_used, im.final_T, im.n_contrib, out_color, st,
+		/* exact exp: the drop-in path; the fused (raw-parameter) path evaluates what its backward evaluates */ !raw));
 	return 0;
 }
 

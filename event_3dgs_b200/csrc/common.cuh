@@ -182,7 +182,7 @@ cudaError_t e3_launch_tile_ranges(size_t R, const uint32_t* tkeys, uint2* ranges
 cudaError_t e3_launch_tile_order(const uint2* ranges, int T, uint32_t* order, cudaStream_t st);
 cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, float* final_T,
-	uint32_t* n_contrib, float* out_color, cudaStream_t st);
+	uint32_t* n_contrib, float* out_color, cudaStream_t st, bool exact = true);
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
 	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st, const float* dL_dpix2 = nullptr);

@@ -133,7 +133,11 @@ __device__ __forceinline__ float eval_power(float dx, float dy, float cx, float 
 	return __fmaf_rn(sum, -0.5f, -__fmul_rn(__fmul_rn(cy, dx), dy));
 }
 
-template <int C>
+// EXACT: the accurate expf of the reference build (forward.cu:336) -- the drop-in path, whose image, final_T and
+// n_contrib are bit-identical to the reference's. !EXACT (fused path, held to the 1e-5 image tolerance instead):
+// ex2.approx of power * log2(e), the very expression the backward blend evaluates, so that the backward sees the
+// alphas the forward blended with; 6 instructions fewer per examined pair.
+template <int C, bool EXACT>
 __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
 	int gx, const uint32_t* __restrict__ point_list, int W, int H, const float4* __restrict__ rec,
 	const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
@@ -195,7 +199,10 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
 				const float power = eval_power(dx, dy, a.z, a.w, b.x);
 				// branch-free: every lane evaluates, selects keep the state of lanes that skip
-				const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
+				float G;
+				if (EXACT) G = expf(power);
+				else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
+				const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
 				const bool contrib = !done && power <= 0.0f && alpha >= 1.0f / 255.0f;
 				const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
 				const bool blend = contrib && test_T >= 0.0001f;
@@ -491,11 +498,13 @@ cudaError_t e3_launch_tile_order(const uint2* ranges, int T, uint32_t* order, cu
 }
 
 cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order, const uint32_t* point_list,
-	const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t st)
+	const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t st, bool exact)
 {
 	const unsigned grid = (unsigned)(f.gx * f.gy);
-	if (f.C == 1) render_fwd_kernel<1><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
-	else render_fwd_kernel<3><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color);
+#define FWD(CH, EX) render_fwd_kernel<CH, EX><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, rec, bg, final_T, n_contrib, out_color)
+	if (f.C == 1) { if (exact) FWD(1, true); else FWD(1, false); }
+	else { if (exact) FWD(3, true); else FWD(3, false); }
+#undef FWD
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }

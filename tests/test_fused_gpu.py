@@ -433,8 +433,12 @@ def test_tight_instance_lists_do_not_change_the_image(cuda_dev):
             st = fused._forward_raw(pc, cam, bgc)
             assert torch.equal(st.radii, ref["radii"])
             assert 0 < st.R < 0.95 * R_ref, (st.R, R_ref)
-            d = float((st.color - ref["render"]).abs().max())
-            assert d < 3e-6, d
+            # the fused forward evaluates exp as ex2.approx (what its backward evaluates), the drop-in one the accurate
+            # expf: per-pixel differences stay at rounding level; a DROPPED contribution would show as >= 1/255 of a
+            # colour on the pixels of a whole tile, an alpha >= 1/255 decision flipped by the last bit on a single pixel
+            diff = (st.color - ref["render"]).abs().amax(0)
+            assert int((diff > 1e-5).sum()) <= 3, int((diff > 1e-5).sum())       # of 24k .. 90k pixels
+            assert float(diff.max()) < 5e-3
 
 
 def test_create_from_pcd_matches_reference_initialisation(cuda_dev):
