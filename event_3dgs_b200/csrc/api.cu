@@ -324,7 +324,7 @@ int e3_rasterize_backward(
 	if (R > 0) {
 		E3BinState b = E3BinState::carve(binning_buffer, (size_t)R);
 		E3_STAGE(E3_STAGE_RENDER_BWD, e3_launch_render_backward(f, im.ranges, im.tile_order, b.val[0], g.rec, background, im.final_T, im.n_contrib,
-			dL_dpix, g.acc, st));
+			dL_dpix, g.acc, st, nullptr, /* the forward's exact exp: see render_bwd_kernel */ true));
 	}
 	E3_STAGE(E3_STAGE_PREPROCESS_BWD, e3_launch_preprocess_backward(f, means3D, radii, shs, nullptr, nullptr, false, false, scales, rotations,
 		cov3D_precomp, viewmatrix, projmatrix, campos, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh,

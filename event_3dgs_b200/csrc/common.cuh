@@ -185,7 +185,8 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, cons
 	uint32_t* n_contrib, float* out_color, cudaStream_t st, bool exact = true);
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order,
 	const uint32_t* point_list, const float4* rec, const float* bg, const float* final_T,
-	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st, const float* dL_dpix2 = nullptr);
+	const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t st, const float* dL_dpix2 = nullptr,
+	bool exact = false);
 
 // knn.cu
 int e3_knn_grid_dim(int P);

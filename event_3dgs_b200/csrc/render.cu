@@ -284,7 +284,12 @@ __device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane)
 // an iteration are the same camera and are rendered once: dL_dpixels is then the SUM of the two loss
 // terms' seeds (all parameter gradients are linear in it), dL_dpixels2 the intensity term alone, whose
 // screen-space gradient is what the reference's densification statistics accumulate (train.py:145,319-320).
-template <int C, bool DUAL>
+// EXACT (drop-in path): G and alpha by the forward's own instruction sequence (accurate expf, the same rounded
+// product), so the backward takes exactly the forward's -- and the reference's -- alpha >= 1/255 decisions. A loss
+// like the event loss (log of the rendered luma) puts seeds of 1e6 times the normal size on nearly black pixels;
+// there a contribution that one pass blends and the other skips on the last bit of alpha decides whole gradient rows.
+// !EXACT (fused path): ex2.approx in both passes, equally consistent with each other.
+template <int C, bool DUAL, bool EXACT>
 __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
 	int gx, const uint32_t* __restrict__ point_list, int W, int H, const float* __restrict__ bg,
 	const float4* __restrict__ rec, const float* __restrict__ final_Ts,
@@ -382,8 +387,9 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			// ex2.approx of power * log2(e): within 5e-7 relative of the forward's accurate expf, far inside
 			// the gradient tolerance (1e-4), 6 instructions shorter per examined pair
 			float G;
-			asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
-			float alpha = fminf(0.99f, b.y * G);
+			if (EXACT) G = expf(power);
+			else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
+			float alpha = fminf(0.99f, __fmul_rn(b.y, G));
 			// contributor = total - 1 - (b0 + j) < last_contributor  <=>  j > jlim
 			const bool valid = (j > jlim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
 			if (!__any_sync(E3_FULL, valid)) continue;
@@ -511,13 +517,15 @@ cudaError_t e3_launch_render_forward(const E3Frame& f, const uint2* ranges, cons
 
 cudaError_t e3_launch_render_backward(const E3Frame& f, const uint2* ranges, const uint32_t* tile_order, const uint32_t* point_list,
 	const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
-	float* acc, cudaStream_t st, const float* dL_dpix2)
+	float* acc, cudaStream_t st, const float* dL_dpix2, bool exact)
 {
 	const unsigned grid = (unsigned)(f.gx * f.gy);
 	if (dL_dpix2 && f.C != 3) return cudaErrorInvalidValue;
-	if (dL_dpix2) render_bwd_kernel<3, true><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, dL_dpix2, acc);
-	else if (f.C == 1) render_bwd_kernel<1, false><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, nullptr, acc);
-	else render_bwd_kernel<3, false><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, nullptr, acc);
+#define BWD(CH, DU, EX) render_bwd_kernel<CH, DU, EX><<<grid, 256, 0, st>>>(ranges, tile_order, f.gx, point_list, f.W, f.H, bg, rec, final_T, n_contrib, dL_dpix, dL_dpix2, acc)
+	if (dL_dpix2) { if (exact) return cudaErrorInvalidValue; BWD(3, true, false); }
+	else if (f.C == 1) { if (exact) BWD(1, false, true); else BWD(1, false, false); }
+	else { if (exact) BWD(3, false, true); else BWD(3, false, false); }
+#undef BWD
 	g_e3_launches += 1;
 	return cudaGetLastError();
 }
