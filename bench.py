@@ -523,7 +523,9 @@ def main():
         # ignored (traffic null) once render.cu has changed since
         tj, traffic_file = load_traffic()
         traffic, traffic_src = None, None
-        kname = "render_bwd_kernel<1, 0>" if "render_bwd_kernel<1, 0>" in tj else "render_bwd_kernel<1>"
+        def kernel_key(prefix):        # template arguments were added over time: <1>, <1, 0>, <1, 0, 0> name the same variant
+            return next((k for k in tj if k.startswith(prefix + ">") or k.startswith(prefix + ", 0")), prefix + ">")
+        kname = kernel_key("render_bwd_kernel<1")
         if cfg_name == "c3" and kname in tj:
             traffic = tj[kname]["dram_bytes_per_launch"]
             traffic_src = "%s (ncu --set full, c3, %s: the single-channel variant, 2 of the 3 launches per step)" % (traffic_file, kname)
@@ -538,7 +540,7 @@ def main():
         # instruction count per launch taken from the same committed ncu capture
         wi = None
         try:
-            k3 = "render_bwd_kernel<3, 0>" if "render_bwd_kernel<3, 0>" in tj else "render_bwd_kernel<3>"
+            k3 = kernel_key("render_bwd_kernel<3")
             if cfg_name == "c3":
                 wi = (tj[k3]["warp_inst_per_launch"] + 2 * tj[kname]["warp_inst_per_launch"]) / 3
         except Exception:
