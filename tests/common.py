@@ -80,11 +80,16 @@ CHAIN_ARRAYS = ("dL_dmeans3D", "dL_dscales", "dL_drotations", "xyz", "scaling", 
 # out of 3M set the maximum. Two such runs against each other are held to ~4x that spread, and to GRAD_TOL on all
 # but 1e-4 of the rows (row-wise check in tests/test_timed_sizes_gpu.py).
 GRAD_TOL_ATOMIC_CHAIN_C5 = {"dL_drotations": 3e-3, "dL_dscales": 1e-3, "dL_dmeans3D": 3e-4}
+# 1M Gaussians at 1280x720 (scene_inputs "trained"): dL_drotations repeats to 1.7e-4 in the reference build itself and
+# ours-against-reference was seen between 1.5e-4 and 3.1e-4 from run to run (one or two rows out of 1M set it): same
+# rule, ~4x the reference's own spread, and GRAD_TOL on all but 1e-4 of the rows.
+GRAD_TOL_ATOMIC_CHAIN_C3 = {"dL_drotations": 1e-3}
 
 
 def grad_tol(name, two_atomic_runs=False, size=None):
     if two_atomic_runs and name in CHAIN_ARRAYS:
-        return GRAD_TOL_ATOMIC_CHAIN_C5.get(name, GRAD_TOL_ATOMIC_CHAIN) if size == "c5" else GRAD_TOL_ATOMIC_CHAIN
+        table = GRAD_TOL_ATOMIC_CHAIN_C5 if size == "c5" else GRAD_TOL_ATOMIC_CHAIN_C3 if size in ("c3", "c3init") else {}
+        return table.get(name, GRAD_TOL_ATOMIC_CHAIN)
     return GRAD_TOL
 
 
