@@ -82,8 +82,10 @@ CHAIN_ARRAYS = ("dL_dmeans3D", "dL_dscales", "dL_drotations", "xyz", "scaling", 
 GRAD_TOL_ATOMIC_CHAIN_C5 = {"dL_drotations": 3e-3, "dL_dscales": 1e-3, "dL_dmeans3D": 3e-4}
 # 1M Gaussians at 1280x720 (scene_inputs "trained"): dL_drotations repeats to 1.7e-4 in the reference build itself and
 # ours-against-reference was seen between 1.5e-4 and 3.1e-4 from run to run (one or two rows out of 1M set it): same
-# rule, ~4x the reference's own spread, and GRAD_TOL on all but 1e-4 of the rows.
-GRAD_TOL_ATOMIC_CHAIN_C3 = {"dL_drotations": 1e-3}
+# rule, ~4x the reference's own spread, and GRAD_TOL on all but 1e-4 of the rows. The leaf gradients of the fused
+# iteration at c3 / c4 (three views summed, through the activations) were seen between 5e-5 and 1.7e-4 (scaling) over
+# 48 comparisons; the reference route against itself is recorded beside them (ref_route_vs_itself/...).
+GRAD_TOL_ATOMIC_CHAIN_C3 = {"dL_drotations": 1e-3, "rotation": 6e-4, "scaling": 6e-4}
 
 
 def grad_tol(name, two_atomic_runs=False, size=None):

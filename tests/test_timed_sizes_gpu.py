@@ -102,6 +102,15 @@ def test_fused_iteration_vs_reference_route_at_timed_sizes(gc, cfg_name):
     loss_r, pkg_r = pl.event_iteration(pc_r, cams[v], cams[v], cams[v + 1], gt, c_r, bg, deblur=deblur, render_fn=render_ref)
     loss_r.backward()
     g_ref = {n: _np(p.grad) for n, p in zip(names, pc_r.leaves() + [c_r])}
+    # the reference route against itself (its float atomics commit in another order): the yardstick for the chain arrays
+    for p in pc_r.leaves() + [c_r]:
+        p.grad = None
+    loss_r2, _ = pl.event_iteration(pc_r, cams[v], cams[v], cams[v + 1], gt, c_r, bg, deblur=deblur, render_fn=render_ref)
+    loss_r2.backward()
+    for n, p in zip(names, pc_r.leaves() + [c_r]):
+        if g_ref[n].any():
+            observe("ref_route_vs_itself/%s/%s" % (cfg_name, n), rel_err(_np(p.grad), g_ref[n], 1e-30))
+    del loss_r2
     vs_ref = _np(pkg_r["viewspace_points"].grad)
     radii_ref = pkg_r["radii"].clone()
     img_ref = pkg_r["render"].detach().clone()
@@ -141,7 +150,10 @@ def test_fused_iteration_vs_reference_route_at_timed_sizes(gc, cfg_name):
                 if a.ndim and a.shape[0] == same.shape[0]:
                     a, b = a[same], b[same]
                 e = observe(key + n, rel_err(a, b, 1e-30))
-                assert e < grad_tol(n, two_atomic_runs=True), (tag, call, n, e)
+                assert e < grad_tol(n, two_atomic_runs=True, size="c3"), (tag, call, n, e)
+                if a.ndim >= 2:     # row-wise: (almost) every row within GRAD_TOL of the array's scale
+                    off = float((np.abs(a - b).reshape(a.shape[0], -1).max(axis=1) >= GRAD_TOL * np.abs(b).max()).mean())
+                    assert observe(key + n + "_rows_off", off) <= 1e-4, (tag, call, n, off)
             # The screen-space gradient comes from the first render alone, so it is not averaged over three views: a
             # Gaussian that is blended in one route and absent from the other (see above) changes the transmittance seen
             # by its neighbours in those pixels. All rows but a handful must agree within GRAD_TOL, those within 2e-3.
