@@ -126,6 +126,22 @@ __device__ __forceinline__ uint32_t lds_u8(uint32_t addr)
 	return v;
 }
 
+// position of the most significant set bit (FLO.U32; m != 0)
+__device__ __forceinline__ int top_bit(uint32_t m)
+{
+	int p;
+	asm("bfind.u32 %0, %1;" : "=r"(p) : "r"(m));
+	return p;
+}
+
+// 1u << p without a constant register (BMSK)
+__device__ __forceinline__ uint32_t bit_at(int p)
+{
+	uint32_t b;
+	asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(b) : "r"(p));
+	return b;
+}
+
 // forward.cu:335 with the reference's contraction
 __device__ __forceinline__ float eval_power(float dx, float dy, float cx, float cy, float cz)
 {
@@ -160,8 +176,9 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 	const float tile_x0 = (float)(tx * E3_TILE_X), tile_y0 = (float)(ty * E3_TILE_Y);
 	const uint2 range = ranges[tile];
 	const int total = (int)(range.y - range.x);
-	bool done = !inside;
-	float T = 1.0f;
+	// T < 0 marks a finished pixel (the reference's `done`): its magnitude is the transmittance it stopped with, and
+	// T (1 - alpha) < 0 fails the blend test from then on without a separate flag. Pixels outside the image start finished.
+	float T = inside ? 1.0f : -1.0f;
 	uint32_t last_contributor = 0;
 	const uint32_t aAB = smem_addr(sAB), aC = smem_addr(sC), aMask = smem_addr(sMask);
 	float Cacc[C];
@@ -169,7 +186,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 	for (int c = 0; c < C; c++) Cacc[c] = 0.f;
 
 	for (int b0 = 0; b0 < total; b0 += kBatchF) {
-		if (__syncthreads_count(done) == E3_TILE_PIX) break;
+		if (__syncthreads_count(T < 0.f) == E3_TILE_PIX) break;
 #pragma unroll
 		for (int l = threadIdx.x; l < kBatchF; l += 256) {
 			const int k = b0 + l;
@@ -186,16 +203,20 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 			}
 		}
 		__syncthreads();
-		if (__all_sync(E3_FULL, done)) continue;    // this warp's 32 pixels are finished
+		if (__all_sync(E3_FULL, T < 0.f)) continue;    // this warp's 32 pixels are finished
 		const int nb = min(kBatchF, total - b0);
 		for (int c0 = 0; c0 < nb; c0 += 32) {
-			const int jj = c0 + lane;
+			// lane l looks at instance c0 + 31 - l: the instances of the chunk that reach this warp's block, first
+			// instance in the top bit, so that one count-leading-zeros yields the next one
+			const int jj = c0 + 31 - lane;
 			uint32_t m = __ballot_sync(E3_FULL, jj < nb && ((lds_u8(aMask + jj) >> w) & 1u));
+			const uint32_t cAB = aAB + 32 * (c0 + 31), cC = aC + 4 * (c0 + 31);
+			const uint32_t contrib_no = (uint32_t)(b0 + c0 + 32);
 			while (m) {
-				const int j = c0 + __ffs(m) - 1;
-				m &= m - 1;
-				const float4 a = lds_f4(aAB + 32 * j);
-				const float4 b = lds_f4(aAB + 32 * j + 16);
+				const int p = top_bit(m);                // instance c0 + 31 - p
+				m ^= bit_at(p);
+				const float4 a = lds_f4(cAB - 32 * p);
+				const float4 b = lds_f4(cAB - 32 * p + 16);
 				const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
 				const float power = eval_power(dx, dy, a.z, a.w, b.x);
 				// branch-free: every lane evaluates, selects keep the state of lanes that skip
@@ -203,22 +224,23 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const uint2* __restrict
 				if (EXACT) G = expf(power);
 				else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
 				const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
-				const bool contrib = !done && power <= 0.0f && alpha >= 1.0f / 255.0f;
+				const bool contrib = power <= 0.0f && alpha >= 1.0f / 255.0f;
 				const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
 				const bool blend = contrib && test_T >= 0.0001f;
-				done = done || (contrib && !blend);
 				const float wgt = __fmul_rn(alpha, b.z);
 				Cacc[0] = blend ? __fmaf_rn(T, wgt, Cacc[0]) : Cacc[0];
 				if (C == 3) {
 					Cacc[1] = blend ? __fmaf_rn(T, __fmul_rn(alpha, b.w), Cacc[1]) : Cacc[1];
-					Cacc[2] = blend ? __fmaf_rn(T, __fmul_rn(alpha, lds_f(aC + 4 * j)), Cacc[2]) : Cacc[2];
+					Cacc[2] = blend ? __fmaf_rn(T, __fmul_rn(alpha, lds_f(cC - 4 * p)), Cacc[2]) : Cacc[2];
 				}
+				last_contributor = blend ? contrib_no - (uint32_t)p : last_contributor;
 				T = blend ? test_T : T;
-				last_contributor = blend ? (uint32_t)(b0 + j + 1) : last_contributor;
+				T = (contrib && !blend) ? -fabsf(T) : T;     // finished (forward.cu:348-352)
 			}
-			if (__all_sync(E3_FULL, done)) break;
+			if (__all_sync(E3_FULL, T < 0.f)) break;
 		}
 	}
+	T = fabsf(T);
 	if (inside) {
 		final_T[pix_id] = T;
 		n_contrib[pix_id] = last_contributor;
@@ -373,13 +395,17 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 		const int j0 = max(0, (total - b0) - wmax);
 		const int jlim = total - 1 - b0 - last_contributor;
 		for (int c0 = (j0 & ~31); c0 < nb; c0 += 32) {
-		const int jj = c0 + lane;
+		// lane l looks at instance c0 + 31 - l: first instance of the chunk in the top bit, so that one
+		// count-leading-zeros yields the next one
+		const int jj = c0 + 31 - lane;
 		uint32_t m = __ballot_sync(E3_FULL, jj < nb && jj >= j0 && ((lds_u8(aMask + jj) >> w) & 1u));
+		const uint32_t cAB = aAB + 32 * (c0 + 31), cC = aC + 4 * (c0 + 31), cId = aId + 4 * (c0 + 31);
+		const int plim = c0 + 31 - jlim;
 		while (m) {
-			const int j = c0 + __ffs(m) - 1;
-			m &= m - 1;
-			const float4 a = lds_f4(aAB + 32 * j);
-			const float4 b = lds_f4(aAB + 32 * j + 16);
+			const int p = top_bit(m);                // instance j = c0 + 31 - p
+			m ^= bit_at(p);
+			const float4 a = lds_f4(cAB - 32 * p);
+			const float4 b = lds_f4(cAB - 32 * p + 16);
 			const float dx = a.x - pixfx, dy = a.y - pixfy;
 			// the forward's own rounding of the power: for a thin, oblique ellipse its terms cancel to a small
 			// difference, and another evaluation order would give another G than the one the forward blended with
@@ -391,7 +417,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			else asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * kLog2e));
 			float alpha = fminf(0.99f, __fmul_rn(b.y, G));
 			// contributor = total - 1 - (b0 + j) < last_contributor  <=>  j > jlim
-			const bool valid = (j > jlim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
+			const bool valid = (p < plim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
 			if (!__any_sync(E3_FULL, valid)) continue;
 
 			// Branch-free from here: a lane without a contribution runs the same arithmetic with
@@ -409,7 +435,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			const float aT = alpha * T;
 			float pc = dL_dpixel[0] * b.z, pc2 = dL_dpixel2[0] * b.z, c2v = 0.f;
 			if (C == 3) {
-				c2v = lds_f(aC + 4 * j);
+				c2v = lds_f(cC - 4 * p);
 				pc = fmaf(dL_dpixel[2], c2v, fmaf(dL_dpixel[1], b.w, pc));
 				if (DUAL) pc2 = fmaf(dL_dpixel2[2], c2v, fmaf(dL_dpixel2[1], b.w, pc2));
 			}
@@ -443,7 +469,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 				u[11] = u[12] = u[13] = u[14] = u[15] = 0.f;
 				warp_reduce16(u, lane);
 				if ((lane & 1) == 0 && my_slot < 11)
-					atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + my_slot, u[0]);
+					atomicAdd(acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE + my_slot, u[0]);
 				continue;
 			}
 			warp_reduce8(v, lane);
@@ -452,10 +478,10 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 				for (int o = 16; o; o >>= 1) v8 += __shfl_xor_sync(E3_FULL, v8, o);
 			}
 			if ((lane & 3) == 0) {
-				float* dst = acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE;
+				float* dst = acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE;
 				if (C == 3 || my_slot < 7) atomicAdd(dst + my_slot, v[0]);
 			}
-			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(aId + 4 * j) * E3_ACC_STRIDE + 8, v8);
+			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE + 8, v8);
 		}
 		}
 	}
