@@ -13,10 +13,11 @@
 //     three 16-byte loads into shared memory (the reference gathers 4+8+16 bytes from three
 //     arrays and fetches colours from global memory per pixel);
 //   * warps whose 32 pixels are all finished skip the batch; the CTA leaves when all are;
-//   * backward: gradients of one Gaussian are reduced across the warp with a reduce-scatter
-//     butterfly (14 shuffles for 9 values instead of 45) and leave the warp as ONE vectorised
-//     red.global per value into a packed 48-byte accumulator -- versus 9 same-address global
-//     atomics per (pixel, Gaussian) pair in the reference (backward.cu:523-554);
+//   * backward: the gradient terms of a (pixel, Gaussian) pair leave the lane as two 16-byte vector
+//     reductions (red.global.add.v4.f32) into a packed 48-byte accumulator row when at most kDirectMax
+//     pixels of the warp's block take part; otherwise the warp sums them first with a reduce-scatter
+//     butterfly (14 shuffles for 9 values instead of 45) and ONE red.global per value leaves the warp
+//     -- versus 9 same-address scalar atomics per (pixel, Gaussian) pair in the reference (backward.cu:523-554);
 //   * backward starts at the tile's last contributing instance instead of the end of the range.
 #include "common.cuh"
 
@@ -33,6 +34,13 @@ namespace {
 // its warp cycles wait at them: the warps of a tile do different amounts of work per batch).
 constexpr int kBatchF = E3_BLEND_BATCH_FWD, kBatchB = E3_BLEND_BATCH_BWD;
 constexpr float kLog2e = 1.4426950408889634f;
+// backward blend: up to this many contributing pixels of a (block, instance) pair send their gradient terms to the
+// accumulator row themselves; with more, the warp sums them first. Measured at c3 (serial backward blends per iteration,
+// ms): 0: 1.35, 4: 1.22, 8: 1.16, 12: 1.12, 16: 1.10, 20: 1.12, 24: 1.21, 32: 1.73 (the L2's reduction rate binds).
+#ifndef E3_BWD_DIRECT_MAX
+#define E3_BWD_DIRECT_MAX 16
+#endif
+constexpr int kDirectMax = E3_BWD_DIRECT_MAX;
 
 __device__ __forceinline__ void pixel_of_thread(int& lx, int& ly)
 {
@@ -140,6 +148,12 @@ __device__ __forceinline__ uint32_t bit_at(int p)
 	uint32_t b;
 	asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(b) : "r"(p));
 	return b;
+}
+
+// 16-byte vector reduction (the accumulator rows are 48 bytes, 16-byte aligned)
+__device__ __forceinline__ void red_add4(float* p, float x, float y, float z, float w)
+{
+	asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 
 // forward.cu:335 with the reference's contraction
@@ -418,7 +432,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			float alpha = fminf(0.99f, __fmul_rn(b.y, G));
 			// contributor = total - 1 - (b0 + j) < last_contributor  <=>  j > jlim
 			const bool valid = (p < plim) && (power <= 0.0f) && (alpha >= 1.0f / 255.0f);
-			if (!__any_sync(E3_FULL, valid)) continue;
+			const uint32_t bal = __ballot_sync(E3_FULL, valid);
+			if (bal == 0u) continue;
 
 			// Branch-free from here: a lane without a contribution runs the same arithmetic with
 			// alpha = G = 0, which leaves its state untouched (T * 1, selects) and makes all of its
@@ -457,31 +472,43 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			v[6] = aT * dL_dpixel[0];
 			v[7] = 0.f;
 			if (C == 3) { v[7] = aT * dL_dpixel[1]; v8 = aT * dL_dpixel[2]; }
+			float u9 = 0.f, u10 = 0.f;
 			if (DUAL) {
 				const float dB2 = pc2 - Bp2;
 				const float g2 = G * (dB2 * T);
 				Bp2 = fmaf(alpha, dB2, Bp2);
+				const float g2x = g2 * dx, g2y = g2 * dy;
+				u9 = fmaf(g2x, a.z, g2y * a.w);
+				u10 = fmaf(g2y, b.x, g2x * a.w);
+			}
+			float* dst = acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE;
+			// A pair that at most kDirectMax pixels of the block take part in: they add their terms themselves, two (three)
+			// 16-byte vector reductions per pixel. Above that the L2's reduction rate would bind and the warp sums first.
+			// (The vote tells the compiler that the branch is uniform.)
+			if (__all_sync(E3_FULL, __popc(bal) <= kDirectMax)) {
+				if (valid) {
+					red_add4(dst, v[0], v[1], v[2], v[3]);
+					red_add4(dst + 4, v[4], v[5], v[6], v[7]);
+					if (DUAL) red_add4(dst + 8, v8, u9, u10, 0.f);
+					else if (C == 3) atomicAdd(dst + 8, v8);
+				}
+			} else if (DUAL) {
 				float u[16];
 #pragma unroll
 				for (int i = 0; i < 8; i++) u[i] = v[i];
-				const float g2x = g2 * dx, g2y = g2 * dy;
-				u[8] = v8; u[9] = fmaf(g2x, a.z, g2y * a.w); u[10] = fmaf(g2y, b.x, g2x * a.w);
+				u[8] = v8; u[9] = u9; u[10] = u10;
 				u[11] = u[12] = u[13] = u[14] = u[15] = 0.f;
 				warp_reduce16(u, lane);
-				if ((lane & 1) == 0 && my_slot < 11)
-					atomicAdd(acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE + my_slot, u[0]);
-				continue;
-			}
-			warp_reduce8(v, lane);
-			if (C == 3) {
+				if ((lane & 1) == 0 && my_slot < 11) atomicAdd(dst + my_slot, u[0]);
+			} else {
+				warp_reduce8(v, lane);
+				if (C == 3) {
 #pragma unroll
-				for (int o = 16; o; o >>= 1) v8 += __shfl_xor_sync(E3_FULL, v8, o);
+					for (int o = 16; o; o >>= 1) v8 += __shfl_xor_sync(E3_FULL, v8, o);
+				}
+				if ((lane & 3) == 0 && (C == 3 || my_slot < 7)) atomicAdd(dst + my_slot, v[0]);
+				if (C == 3 && lane == 1) atomicAdd(dst + 8, v8);
 			}
-			if ((lane & 3) == 0) {
-				float* dst = acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE;
-				if (C == 3 || my_slot < 7) atomicAdd(dst + my_slot, v[0]);
-			}
-			if (C == 3 && lane == 1) atomicAdd(acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE + 8, v8);
 		}
 		}
 	}

@@ -68,10 +68,17 @@ def scaled_err(a, b, f=1e-2):
 # ---- tolerances (BASELINE.md section 5 holds the table and its justification) ----
 IMG_TOL = 1e-5          # image, final_T, loss: relative to the array maximum
 GRAD_TOL = 1e-4         # every gradient array against the fp64-accumulating oracle / the reference build
-# Two fp32 runs whose float atomics commit in different orders (ours against the reference build on large
-# scenes, or separately executed iterations): the arrays behind the conic -> covariance chain repeat only to
-# ~1.2e-4 in the reference build itself (profiles/r1_grad_run_to_run_spread.json).
-GRAD_TOL_ATOMIC_CHAIN = 3e-4
+# Two fp32 runs whose float atomics commit in different orders (ours against the reference build, or separately
+# executed iterations): the arrays behind the conic -> covariance chain are sums of per-pixel terms that cancel, and
+# repeat only to ~1.2e-4 (20k Gaussians) .. 1.6e-4 (c3) in the reference build itself
+# (profiles/r1_grad_run_to_run_spread.json, profiles/r2_parity_observed.json ref_vs_ref/...). Since the backward blend
+# sends the terms of sparsely covered pairs to the accumulator as per-pixel vector reductions (as the reference does for
+# every pair), ours repeats itself to the same level (ours_vs_ours/...), and two such runs differ by up to 3.4e-4 on
+# `scaling` under the L1 + SSIM seeds (20k Gaussians, 346x260; 2 of 11 runs above 3e-4).
+GRAD_TOL_ATOMIC_CHAIN = 6e-4
+# one such run against the exact (fp64-accumulating) oracle: the reference build lands at up to 7e-5 on the test scenes,
+# ours between 1e-5 and 7e-5 from run to run
+GRAD_TOL_CHAIN_VS_EXACT = 2e-4
 CHAIN_ARRAYS = ("dL_dmeans3D", "dL_dscales", "dL_drotations", "xyz", "scaling", "rotation")
 
 
@@ -89,10 +96,17 @@ GRAD_TOL_ATOMIC_CHAIN_C3 = {"dL_drotations": 1e-3, "rotation": 6e-4, "scaling": 
 
 
 def grad_tol(name, two_atomic_runs=False, size=None):
+    """two_atomic_runs: both sides are fp32 runs with float atomics; otherwise ours against the fp64 oracle."""
+    if not two_atomic_runs and name in CHAIN_ARRAYS:
+        return GRAD_TOL_CHAIN_VS_EXACT
     if two_atomic_runs and name in CHAIN_ARRAYS:
         table = GRAD_TOL_ATOMIC_CHAIN_C5 if size == "c5" else GRAD_TOL_ATOMIC_CHAIN_C3 if size in ("c3", "c3init") else {}
         return table.get(name, GRAD_TOL_ATOMIC_CHAIN)
     return GRAD_TOL
+
+
+# order of GaussianParams.leaves() (+ the event threshold c)
+LEAF_NAMES = ["xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity", "c"]
 
 
 OBSERVED = {}

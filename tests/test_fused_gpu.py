@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import torch
 
-from tests.common import GRAD_TOL, grad_tol, rel_err
+from tests.common import GRAD_TOL, LEAF_NAMES, grad_tol, observe, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -175,8 +175,8 @@ def test_dedupe_identical_views_gives_same_loss_and_gradients(cuda_dev, sh_degre
         gb = [p.grad.clone() for p in leaves]
         assert len(pb["num_rendered"]) == 2
         assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item()), no_sync
-        for a, b in zip(ga, gb):
-            assert rel_err(b.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4, no_sync
+        for n, a, b in zip(LEAF_NAMES, ga, gb):
+            assert rel_err(b.cpu().numpy(), a.cpu().numpy(), 1e-20) < grad_tol(n, two_atomic_runs=True), (no_sync, n)
         # the screen-space gradient of the first render (densification statistics, train.py:319-320) is the
         # intensity term's alone in both: the shared view's backward blend carries it as a second seed
         va, vb = pa["viewspace_points"].grad, pb["viewspace_points"].grad
@@ -270,7 +270,8 @@ def test_frame_iteration_matches_dropin_autograd(cuda_dev):
         # two fp32 pipelines whose activations / SH colours round differently (ATen vs in-kernel): a
         # borderline alpha >= 1/255 or radius decision may flip for single Gaussians
         for n, a, b in zip(("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity"), ga, gb):
-            assert rel_err(b.cpu().numpy(), a.cpu().numpy()) < grad_tol(n, two_atomic_runs=True), (gray, n)
+            e = observe("frame_fused_vs_dropin/%s/%s" % ("gray" if gray else "rgb", n), rel_err(b.cpu().numpy(), a.cpu().numpy()))
+            assert e < grad_tol(n, two_atomic_runs=True), (gray, n, e)
 
 
 def test_accumulate_over_view_pairs(cuda_dev):
@@ -308,15 +309,15 @@ def test_no_sync_workspace_path_and_overflow_recovery(cuda_dev):
     assert pb["num_rendered"] == pa["num_rendered"]
     assert torch.equal(pb["render"], img_a) and torch.equal(pb["radii"], pa["radii"])
     assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
-    for p, a in zip(leaves, ga):
-        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    for n, p, a in zip(LEAF_NAMES, leaves, ga):
+        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < grad_tol(n, two_atomic_runs=True), n
     # too small a workspace: the step notices, enlarges it and repeats itself
     ws.resize(4096)
     lc, pc_pkg = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True)
     assert pc._e3_ws.cap >= max(pa["num_rendered"])
     assert torch.equal(pc_pkg["render"], img_a)
-    for p, a in zip(leaves, ga):
-        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+    for n, p, a in zip(LEAF_NAMES, leaves, ga):
+        assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < grad_tol(n, two_atomic_runs=True), n
 
 
 def test_lazy_check_runs_ahead_and_reports_overflow_late(cuda_dev):
@@ -334,8 +335,8 @@ def test_lazy_check_runs_ahead_and_reports_overflow_late(cuda_dev):
         lb, pb = fused.event_iteration_backward(pc, cams[3], cams[3], cams[4], gt, c, bg, return_pkg=True, lazy_check=True)
         assert abs(la.item() - lb.item()) <= 1e-6 * abs(la.item())
         assert torch.equal(pb["render"], pa["render"])
-        for p, a in zip(leaves, ga):
-            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < 1e-4
+        for n, p, a in zip(LEAF_NAMES, leaves, ga):
+            assert rel_err(p.grad.cpu().numpy(), a.cpu().numpy(), 1e-20) < grad_tol(n, two_atomic_runs=True), n
     assert ws.pending[0] and ws.pending[1]                 # two iterations are still unchecked
     assert ws.drain() == pa["num_rendered"] and not any(ws.pending)
     # overflow: nothing is raised by the call that overflows, nor by the next one ...

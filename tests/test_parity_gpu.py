@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 import torch
 
-from tests.common import grad_tol, observe, oracle_forward, rel_err, scaled_err, scene_inputs, smooth_dL
+from tests.common import CHAIN_ARRAYS, LEAF_NAMES, grad_tol, observe, oracle_forward, rel_err, scaled_err, scene_inputs, smooth_dL
 
 pytestmark = pytest.mark.gpu
 
@@ -98,7 +98,8 @@ def test_backward_vs_reference_cuda_and_oracle(gc, P, W, H, seed, kind, bg):
     fl = {k: 0.0 for k in keys}
     fl["dL_drotations"] = 1e-3 * float(np.abs(go["dL_dscales"]).max()) * float(np.abs(inp["scales"]).max())
     for k in keys:
-        assert rel_err(_np(g[k]).reshape(go[k].shape), go[k], fl[k]) < GRAD_TOL, ("oracle", k)
+        e = observe("vs_oracle/%dx%d_%s_%d/%s" % (W, H, kind, seed, k), rel_err(_np(g[k]).reshape(go[k].shape), go[k], fl[k]))
+        assert e < grad_tol(k), ("oracle", k, e)
         # scale-aware companion (tests/common.scaled_err): an element is held against |itself| + 1 % of the array maximum,
         # so rows two orders of magnitude below the maximum are checked too, not only the largest ones
         if not (k == "dL_drotations" and kind == "init"):
@@ -108,9 +109,11 @@ def test_backward_vs_reference_cuda_and_oracle(gc, P, W, H, seed, kind, bg):
         ref, R, out, radii = gc.ref_forward(inp)
         gr = ref.backward(gc.T(dL))
         for k in keys:
-            assert rel_err(_np(g[k]).reshape(go[k].shape), _np(gr[k]).reshape(go[k].shape), fl[k]) < GRAD_TOL, ("ref", k)
+            e = observe("vs_ref/%dx%d_%s_%d/%s" % (W, H, kind, seed, k), rel_err(_np(g[k]).reshape(go[k].shape), _np(gr[k]).reshape(go[k].shape), fl[k]))
+            assert e < grad_tol(k, two_atomic_runs=True), ("ref", k, e)
             # the reference itself (float atomics) is held to the same bar against the fp64-accumulating oracle
-            assert rel_err(_np(gr[k]).reshape(go[k].shape), go[k], fl[k]) < GRAD_TOL, ("ref-vs-oracle", k)
+            e = observe("ref_vs_oracle/%dx%d_%s_%d/%s" % (W, H, kind, seed, k), rel_err(_np(gr[k]).reshape(go[k].shape), go[k], fl[k]))
+            assert e < grad_tol(k), ("ref-vs-oracle", k, e)
     # rows of culled Gaussians are written as zeros (outputs are not pre-zeroed by the caller)
     culled = ~(fw["radii"] > 0)
     for k in keys:
@@ -123,8 +126,8 @@ def test_backward_twice_gives_same_result(gc):
     fw = gc.ours_forward(inp)
     g1 = gc.ours_backward(fw, inp, dL)
     g2 = gc.ours_backward(fw, inp, dL)
-    for k in g1:
-        assert rel_err(_np(g2[k]), _np(g1[k])) < 1e-5, k
+    for k in g1:         # the accumulator is left clean; what remains is the order of the float atomics
+        assert rel_err(_np(g2[k]), _np(g1[k])) < (grad_tol(k, two_atomic_runs=True) if k in CHAIN_ARRAYS else 1e-5), k
 
 
 def test_sh_colours_and_precomputed_cov3d(gc):
@@ -141,7 +144,7 @@ def test_sh_colours_and_precomputed_cov3d(gc):
         g = gc.ours_backward(fw, inp, dL)
         go = ro.rasterize_backward(o, dL)
         for k in ["dL_dsh", "dL_dmeans3D", "dL_dopacity", "dL_dscales", "dL_drotations"]:
-            assert rel_err(_np(g[k]).reshape(go[k].shape), go[k]) < GRAD_TOL, (deg, k)
+            assert rel_err(_np(g[k]).reshape(go[k].shape), go[k]) < grad_tol(k), (deg, k)
         if ref_cuda.available():
             ref, R, out, radii = gc.ref_forward(inp, use_sh=True, sh_degree=deg)
             assert rel_err(_np(fw["color"]), _np(out)) < IMG_TOL
@@ -170,7 +173,7 @@ def test_single_channel_matches_luma_of_rgb(gc):
     g3 = gc.ours_backward(fw3, inp, w[:, None, None] * dY)
     assert rel_err(_np(g1["dL_dcolors"]) * w[None, :], _np(g3["dL_dcolors"])) < GRAD_TOL
     for k in ["dL_dmeans3D", "dL_dopacity", "dL_dscales", "dL_drotations"]:
-        assert rel_err(_np(g1[k]), _np(g3[k])) < GRAD_TOL, k
+        assert rel_err(_np(g1[k]), _np(g3[k])) < grad_tol(k, two_atomic_runs=True), k
 
 
 def test_edge_cases(gc):
@@ -396,8 +399,8 @@ def test_dropin_no_sync_forward_matches_and_detects_overflow(gc):
             img, radii, grads, vs = run(c)
             assert torch.equal(img.view(torch.int32), ref[i][0].view(torch.int32)), i
             assert torch.equal(radii, ref[i][1])
-            for a, b in zip(grads, ref[i][2]):
-                assert rel_err(_np(a), _np(b), 1e-12) < 1e-4
+            for n, a, b in zip(LEAF_NAMES, grads, ref[i][2]):       # two runs, two orders of the float atomics
+                assert rel_err(_np(a), _np(b), 1e-12) < grad_tol(n, two_atomic_runs=True), n
             assert rel_err(_np(vs), _np(ref[i][3])) < 1e-4
         rz.verify_no_sync(True)
         assert rz._cap_stats[key][0] == len(cams) and rz._cap_stats[key][1] > 0
