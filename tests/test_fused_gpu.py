@@ -270,8 +270,16 @@ def test_frame_iteration_matches_dropin_autograd(cuda_dev):
         # two fp32 pipelines whose activations / SH colours round differently (ATen vs in-kernel): a
         # borderline alpha >= 1/255 or radius decision may flip for single Gaussians
         for n, a, b in zip(("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity"), ga, gb):
-            e = observe("frame_fused_vs_dropin/%s/%s" % ("gray" if gray else "rgb", n), rel_err(b.cpu().numpy(), a.cpu().numpy()))
-            assert e < grad_tol(n, two_atomic_runs=True), (gray, n, e)
+            an, bn = a.cpu().numpy(), b.cpu().numpy()
+            e = observe("frame_fused_vs_dropin/%s/%s" % ("gray" if gray else "rgb", n), rel_err(bn, an))
+            # The L1 part of this loss seeds every pixel with +-1/N: the per-pixel terms of a Gaussian cancel almost
+            # completely, and the order of the float atomics shows in what is left (two runs: up to 4.2e-4 on `scaling`,
+            # 15 runs). Chain arrays: 2.5x the two-run bar on the maximum, GRAD_TOL on all but 1e-3 of the rows.
+            chain = n in ("xyz", "scaling", "rotation")
+            assert e < (2.5 if chain else 1.0) * grad_tol(n, two_atomic_runs=True), (gray, n, e)
+            if an.any():
+                off = float((np.abs(an - bn).reshape(an.shape[0], -1).max(axis=1) >= GRAD_TOL * np.abs(an).max()).mean())
+                assert observe("frame_fused_vs_dropin/%s/%s_rows_off" % ("gray" if gray else "rgb", n), off) <= 1e-3, (gray, n, off)
 
 
 def test_accumulate_over_view_pairs(cuda_dev):
