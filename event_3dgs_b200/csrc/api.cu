@@ -176,7 +176,8 @@ static int forward_impl(
 
 	// depth order of the Gaussians (culled ones carry key 0xffffffff and emit nothing)
 	int dres = 0;
-	E3_STAGE(E3_STAGE_DEPTH_SORT, e3_radix_sort_pairs(g.dkey, g.dval, (size_t)P, 32, g.sort_counts, g.scan_tmp, 0, &dres, st));
+	// culled Gaussians carry the key 0xffffffff and no instances: where they end up in the order is irrelevant
+	E3_STAGE(E3_STAGE_DEPTH_SORT, e3_radix_sort_pairs(g.dkey, g.dval, (size_t)P, 32, g.sort_counts, g.scan_tmp, 0, &dres, st, nullptr, true));
 	const uint32_t* order = g.dval[dres];
 	// instance offsets in depth order; grand total = num_rendered
 	E3_STAGE(E3_STAGE_OFFSETS_SCAN, e3_exclusive_scan_u32(g.tiles_touched, order, g.offsets, (size_t)P, g.scan_tmp,
@@ -516,6 +517,18 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 			v.cam_pos, v.tan_fovx, v.tan_fovy, v.out_color, v.radii, 0, sts[k]);
 		if (rc) return rc;
 	}
+	if (a->grad_multicast_delta != 0 && !a->accumulate) return E3_ERR_BAD_ARGUMENT;   // the caller zeroes and fences (see header)
+	// the gradient rows are zeroed behind this stream's own forward, while the other views still blend: off the
+	// critical path between the loss and the backward blends
+	if (!a->accumulate && a->P > 0) {
+		const size_t P = (size_t)a->P;
+		E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_features_dc, 0, P * 3 * sizeof(float), main_st));
+		if (a->d_features_rest && a->active_sh_degree > 0) E3_CHECK(cudaMemsetAsync(a->d_features_rest, 0, P * 45 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_opacity_logits, 0, P * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_log_scales, 0, P * 3 * sizeof(float), main_st));
+		E3_CHECK(cudaMemsetAsync(a->d_raw_rotations, 0, P * 4 * sizeof(float), main_st));
+	}
 	for (int k = 1; k < 3; k++) {
 		E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
 		E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
@@ -531,16 +544,6 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	// ---- per view, on its own stream: backward blend, then the gradient accumulation. The three
 	// views add into the same (zeroed) gradient tensors with vector reductions, so nothing serialises
 	// behind the blends and the latency-bound accumulation kernels fill the gaps the blends leave. ----
-	if (a->grad_multicast_delta != 0 && !a->accumulate) return E3_ERR_BAD_ARGUMENT;   // the caller zeroes and fences (see header)
-	if (!a->accumulate) {
-		const size_t P = (size_t)a->P;
-		E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_features_dc, 0, P * 3 * sizeof(float), main_st));
-		if (a->d_features_rest && a->active_sh_degree > 0) E3_CHECK(cudaMemsetAsync(a->d_features_rest, 0, P * 45 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_opacity_logits, 0, P * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_log_scales, 0, P * 3 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_raw_rotations, 0, P * 4 * sizeof(float), main_st));
-	}
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
 	for (int k = 0; k < 3; k++) {

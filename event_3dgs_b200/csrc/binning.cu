@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256) radix_hist_all_kernel(const uint32_t* __r
 __global__ void __launch_bounds__(E3_SORT_THREADS, E3_SORT_MIN_BLOCKS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
 	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
 	size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist, volatile uint32_t* lookback,
-	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev)
+	uint32_t* __restrict__ tile_counter, const uint32_t* __restrict__ n_dev, int padding_bin)
 {
 	const uint32_t ntiles = gridDim.x;     // the launch is sized for the capacity, the descriptor arrays with it
 	if (n_dev) n = min(n, (size_t)*n_dev);
@@ -156,7 +156,11 @@ __global__ void __launch_bounds__(E3_SORT_THREADS, E3_SORT_MIN_BLOCKS) radix_one
 	// is the identity permutation, so the tile is copied to the other buffer without ranking or
 	// look-back. Typical for the top byte of the depth keys (sign + 7 exponent bits: all depths of a
 	// scene inside [2^k, 4 * 2^k)).
-	if (__syncthreads_or(threadIdx.x <= mask && ghist[threadIdx.x] == (uint32_t)n && n > 0)) {
+	// padding_bin >= 0 (last pass only): the keys of that bin are all-ones padding whose place in the result does not
+	// matter (the depth keys of culled Gaussians). The lower passes have already put them behind everything else, so
+	// the pass is the identity as well when the real keys agree on the digit.
+	if (__syncthreads_or(threadIdx.x <= mask && n > 0 && (ghist[threadIdx.x] == (uint32_t)n ||
+			(padding_bin >= 0 && ghist[threadIdx.x] + ghist[padding_bin] == (uint32_t)n)))) {
 		const size_t t0 = (size_t)blockIdx.x * E3_SORT_TILE;
 		for (size_t k = t0 + threadIdx.x; k < min(n, t0 + (size_t)E3_SORT_TILE); k += E3_SORT_THREADS) {
 			keys_out[k] = keys_in[k];
@@ -357,7 +361,8 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 }
 
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev)
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev,
+	bool all_ones_is_padding)
 {
 	(void)scan_tmp;
 	int cur = start_buf;
@@ -383,7 +388,8 @@ cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, 
 		radix_hist_all_kernel<<<hgrid, 256, 0, st>>>(keys[cur], n, plan, ghist, n_dev);
 		for (int p = 0; p < plan.npass; p++) {
 			radix_onesweep_kernel<<<(unsigned)nblk, E3_SORT_THREADS, 0, st>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * e3_sort_desc_words(n), tile_counter + p, n_dev);
+				plan.shift[p], (1u << plan.bits[p]) - 1u, ghist + p * 256, lookback + (size_t)p * e3_sort_desc_words(n), tile_counter + p, n_dev,
+				(all_ones_is_padding && p == plan.npass - 1 && plan.shift[p] + plan.bits[p] == 32) ? (int)((1u << plan.bits[p]) - 1u) : -1);
 			cur ^= 1;
 		}
 		g_e3_launches += 1 + plan.npass;

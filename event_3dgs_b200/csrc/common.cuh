@@ -170,9 +170,13 @@ cudaError_t e3_exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint3
 // Stable LSD radix sort of (key,val) pairs over key bits [0,end_bit). The input is read from
 // ping-pong buffer `start_buf`; *result_buf receives the index (0/1) of the buffer that holds
 // the result. e3_radix_passes() tells how many passes (buffer flips) that takes.
+// all_ones_is_padding (32-bit keys): entries with key 0xffffffff are padding whose position in the result is
+// irrelevant to the caller; they end up behind all other keys, but not necessarily in index order among keys
+// that share their low bits.
 static inline int e3_radix_passes(int end_bit) { return (end_bit + 7) / 8; }
 cudaError_t e3_radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], size_t n, int end_bit,
-	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev = nullptr);
+	uint32_t* counts, uint32_t* scan_tmp, int start_buf, int* result_buf, cudaStream_t st, const uint32_t* n_dev = nullptr,
+	bool all_ones_is_padding = false);
 cudaError_t e3_launch_emit_instances(int P, const uint32_t* order, const uint32_t* offsets,
 	const uint32_t* tiles_touched, const uint2* rect, int gx, uint32_t* tkeys, uint32_t* vals, uint32_t cap,
 	cudaStream_t st);

@@ -484,8 +484,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 			float* dst = acc + (size_t)lds_u32(cId - 4 * p) * E3_ACC_STRIDE;
 			// A pair that at most kDirectMax pixels of the block take part in: they add their terms themselves, two (three)
 			// 16-byte vector reductions per pixel. Above that the L2's reduction rate would bind and the warp sums first.
-			// (The vote tells the compiler that the branch is uniform.)
-			if (__all_sync(E3_FULL, __popc(bal) <= kDirectMax)) {
+			if (__popc(bal) <= kDirectMax) {
 				if (valid) {
 					red_add4(dst, v[0], v[1], v[2], v[3]);
 					red_add4(dst + 4, v[4], v[5], v[6], v[7]);
