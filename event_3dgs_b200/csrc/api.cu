@@ -425,6 +425,7 @@ int e3_event_loss(int width, int height, const float* image, const float* image_
 		!scratch || scratch_bytes < 8 * sizeof(double) || (reinterpret_cast<size_t>(scratch) & 7) || !d_image || !d_image_now ||
 		!d_image_next || !out5)
 		return E3_ERR_BAD_ARGUMENT;
+	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_gt_fraction((size_t)width * height, gt_now, gt_next, gt_is_u8, static_cast<double*>(scratch), st));
 	E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_loss((size_t)width * height, image, image_now, image_next, gt_now, gt_next,
 		gt_intensity, gt_blur, gt_is_u8, c, upstream, event_channels, static_cast<double*>(scratch), d_image, d_image_now, d_image_next, out5, st));
 	return 0;
@@ -458,7 +459,8 @@ int e3_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, void* scratch
 // Two side streams and their fork/join events per device: the three views of an iteration are
 // independent until the loss and again until the gradient accumulation, and at event-camera
 // resolutions one view alone does not fill the 148 SMs (374 tiles at 346x260).
-struct ViewStreams { cudaStream_t side[2]; cudaEvent_t fork, join[2]; bool ok; };
+// aux: what needs no render (zeroing the gradient rows, the GT-only part of the loss) runs beside the forwards
+struct ViewStreams { cudaStream_t side[2], aux; cudaEvent_t fork, join[2], aux_join; bool ok; };
 static ViewStreams g_view_streams[64];
 static std::mutex g_view_streams_mu;
 
@@ -476,6 +478,8 @@ static cudaError_t view_streams(ViewStreams** out)
 			if ((e = cudaEventCreateWithFlags(&v.join[i], cudaEventDisableTiming)) != cudaSuccess) return e;
 		}
 		if ((e = cudaEventCreateWithFlags(&v.fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+		if ((e = cudaStreamCreateWithFlags(&v.aux, cudaStreamNonBlocking)) != cudaSuccess) return e;
+		if ((e = cudaEventCreateWithFlags(&v.aux_join, cudaEventDisableTiming)) != cudaSuccess) return e;
 		v.ok = true;
 	}
 	*out = &v;
@@ -503,11 +507,35 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 			if (!armed) return;
 			for (int k = 0; k < 2; k++)
 				if (cudaEventRecord(v->join[k], v->side[k]) == cudaSuccess) cudaStreamWaitEvent(m, v->join[k], 0);
+			if (cudaEventRecord(v->aux_join, v->aux) == cudaSuccess) cudaStreamWaitEvent(m, v->aux_join, 0);
 		}
 	} join_guard{ vs, main_st };
-	// ---- three forwards, one stream each ----
+	if (a->grad_multicast_delta != 0 && !a->accumulate) return E3_ERR_BAD_ARGUMENT;   // the caller zeroes and fences (see header)
+	if (a->P > 0 && (!a->gt_now || !a->gt_next || !a->gt_intensity || !a->c || !a->loss_scratch || (reinterpret_cast<size_t>(a->loss_scratch) & 7) ||
+		!a->out5 || !a->views[0].seed || !a->views[1].seed || !a->views[2].seed))
+		return E3_ERR_BAD_ARGUMENT;
+	// ---- three forwards, one stream each; beside them what needs no render: the gradient rows are zeroed and the
+	// GT-only part of the loss is taken, off the critical path between the forwards and the backward blends ----
 	E3_CHECK(cudaEventRecord(vs->fork, main_st));
 	for (int k = 1; k < 3; k++) E3_CHECK(cudaStreamWaitEvent(sts[k], vs->fork, 0));
+	if (a->P > 0) {
+		const int debug = 0;
+		cudaStream_t st = vs->aux;
+		E3_CHECK(cudaStreamWaitEvent(st, vs->fork, 0));
+		if (a->wait_before_loss_event) E3_CHECK(cudaStreamWaitEvent(st, (cudaEvent_t)a->wait_before_loss_event, 0));
+		E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_gt_fraction((size_t)a->width * a->height, a->gt_now, a->gt_next, a->gt_is_u8,
+			static_cast<double*>(a->loss_scratch), st));
+		if (!a->accumulate) {
+			const size_t P = (size_t)a->P;
+			E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), st));
+			E3_CHECK(cudaMemsetAsync(a->d_features_dc, 0, P * 3 * sizeof(float), st));
+			if (a->d_features_rest && a->active_sh_degree > 0) E3_CHECK(cudaMemsetAsync(a->d_features_rest, 0, P * 45 * sizeof(float), st));
+			E3_CHECK(cudaMemsetAsync(a->d_opacity_logits, 0, P * sizeof(float), st));
+			E3_CHECK(cudaMemsetAsync(a->d_log_scales, 0, P * 3 * sizeof(float), st));
+			E3_CHECK(cudaMemsetAsync(a->d_raw_rotations, 0, P * 4 * sizeof(float), st));
+		}
+		E3_CHECK(cudaEventRecord(vs->aux_join, st));
+	}
 	for (int k = 0; k < 3; k++) {
 		if (shared && k == 1) continue;
 		const e3_view& v = a->views[k];
@@ -517,18 +545,6 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 			v.cam_pos, v.tan_fovx, v.tan_fovy, v.out_color, v.radii, 0, sts[k]);
 		if (rc) return rc;
 	}
-	if (a->grad_multicast_delta != 0 && !a->accumulate) return E3_ERR_BAD_ARGUMENT;   // the caller zeroes and fences (see header)
-	// the gradient rows are zeroed behind this stream's own forward, while the other views still blend: off the
-	// critical path between the loss and the backward blends
-	if (!a->accumulate && a->P > 0) {
-		const size_t P = (size_t)a->P;
-		E3_CHECK(cudaMemsetAsync(a->d_xyz, 0, P * 3 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_features_dc, 0, P * 3 * sizeof(float), main_st));
-		if (a->d_features_rest && a->active_sh_degree > 0) E3_CHECK(cudaMemsetAsync(a->d_features_rest, 0, P * 45 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_opacity_logits, 0, P * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_log_scales, 0, P * 3 * sizeof(float), main_st));
-		E3_CHECK(cudaMemsetAsync(a->d_raw_rotations, 0, P * 4 * sizeof(float), main_st));
-	}
 	for (int k = 1; k < 3; k++) {
 		E3_CHECK(cudaEventRecord(vs->join[k - 1], sts[k]));
 		E3_CHECK(cudaStreamWaitEvent(main_st, vs->join[k - 1], 0));
@@ -536,11 +552,16 @@ int e3_event_iteration(const e3_event_iteration_args* a, void* stream)
 	if (a->forwards_done_event) E3_CHECK(cudaEventRecord((cudaEvent_t)a->forwards_done_event, main_st));
 	if (a->P == 0) return 0;
 	if (a->wait_before_loss_event) E3_CHECK(cudaStreamWaitEvent(main_st, (cudaEvent_t)a->wait_before_loss_event, 0));
-	int rc = e3_event_loss(a->width, a->height, a->views[0].out_color, a->views[shared ? 0 : 1].out_color, a->views[2].out_color, a->gt_now,
-		a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c, a->loss_upstream != 0.f ? a->loss_upstream : 1.0f,
-		shared ? E3_EVENT_SHARED_FIRST_VIEW : a->views[1].channels, a->loss_scratch, 64,
-		a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, main_st);
-	if (rc) return rc;
+	E3_CHECK(cudaStreamWaitEvent(main_st, vs->aux_join, 0));
+	{
+		const int debug = 0;
+		cudaStream_t st = main_st;
+		E3_STAGE(E3_STAGE_EVENT_LOSS, e3_launch_event_loss((size_t)a->width * a->height, a->views[0].out_color,
+			a->views[shared ? 0 : 1].out_color, a->views[2].out_color, a->gt_now, a->gt_next, a->gt_intensity, a->gt_blur, a->gt_is_u8, a->c,
+			a->loss_upstream != 0.f ? a->loss_upstream : 1.0f, shared ? E3_EVENT_SHARED_FIRST_VIEW : a->views[1].channels,
+			static_cast<double*>(a->loss_scratch), a->views[0].seed, a->views[1].seed, a->views[2].seed, a->out5, st));
+	}
+	int rc = 0;
 	// ---- per view, on its own stream: backward blend, then the gradient accumulation. The three
 	// views add into the same (zeroed) gradient tensors with vector reductions, so nothing serialises
 	// behind the blends and the latency-bound accumulation kernels fill the gaps the blends leave. ----

@@ -160,6 +160,7 @@ cudaError_t e3_launch_preprocess_backward(const E3Frame& f, const float* means3D
 	const float* campos, const E3GeomState& g, float* dL_dmean2D, float* dL_dconic,
 	float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* d_frest,
 	float* dL_dscale, float* dL_drot, cudaStream_t st);
+cudaError_t e3_launch_event_gt_fraction(size_t N, const void* gt_now, const void* gt_next, int gt_is_u8, double* sums, cudaStream_t st);
 cudaError_t e3_launch_event_loss(size_t N, const float* image, const float* image_now, const float* image_next,
 	const void* gt_now, const void* gt_next, const void* gt_int, const void* gt_blur, int gt_is_u8, const float* c_ptr,
 	float upstream, int event_channels, double* sums, float* d_image, float* d_now, float* d_next, float* out, cudaStream_t st);
