@@ -232,7 +232,7 @@ E3_API int e3_rasterize_backward_raw_dual(
 	int debug, void* stream);
 
 /* Event loss of train.py:165-203 (with utils/loss_utils.py:24-28, 234-249, 270-271), value and
- * backward seeds in two streaming kernels. Inputs are [3,H,W] float images: the three renders
+ * backward seeds in one streaming pass over the renders behind a pass over the two GT event frames. Inputs are [3,H,W] float images: the three renders
  * (image = intensity view, image_now / image_next = event views index / index+1), the GT event
  * frames, the GT intensity frame and, for --deblur, the blurry frame (else NULL). The four GT
  * frames are float32 in [0,1] (gt_is_u8 = 0) or the raw 8-bit pixels (gt_is_u8 = 1; the kernel
