@@ -430,7 +430,8 @@ typedef struct e3_event_iteration_args {
 	                                cross-rank barrier, runs the iteration(s), passes a second barrier, and
 	                                then holds the sum over all ranks. */
 } e3_event_iteration_args;
-/* Not re-entrant per device: the two side streams and their fork/join events exist once per device, so one
+/* Not re-entrant per device: the three side streams (two views, and one for what needs no render: zeroing the gradient
+ * rows, the GT-only part of the loss) and their fork/join events exist once per device, so one
  * host thread per GPU may be inside this call at a time (the one-process-per-GPU model of SURVEY.md 8b). On any
  * return, error returns included, `stream` is ordered behind all work the call gave to its side streams. */
 E3_API int e3_event_iteration(const e3_event_iteration_args* args_host, void* stream);
