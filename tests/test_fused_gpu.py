@@ -96,6 +96,46 @@ def test_event_loss_kernel_vs_numpy_oracle_and_golden(cuda_dev):
     assert abs(o8[0].item() - of[0].item()) <= 1e-7 * abs(of[0].item())
 
 
+def test_event_loss_scalar_path_odd_sizes(cuda_dev):
+    """The event loss takes four pixels per thread when H*W is a multiple of 4 and every plane is 16-byte aligned, else one
+    pixel per thread: an odd-sized frame (and, through it, misaligned channel planes) against the numpy oracle, with
+    fp32 and 8-bit GT frames, with and without the blurry frame, for luma and RGB event views."""
+    from event_3dgs_b200 import fused
+    from oracle import loss_oracle as lo
+    rng = np.random.default_rng(3)
+    for (H, W) in ((37, 53), (31, 44), (64, 36)):            # N = 1961, 1364 (N % 4 == 0), 2304
+        for deblur in (False, True):
+            for ev_c in (3, 1):
+                f = lambda ch: rng.uniform(0.02, 0.98, (ch, H, W)).astype(np.float32)
+                g8 = {k: rng.integers(0, 256, (3, H, W), dtype=np.uint8) for k in ("event_now", "event_next", "intensity", "blurry")}
+                g8["event_next"][:, : H // 2] = g8["event_now"][:, : H // 2]          # pixels without a GT event
+                gf = {k: (v.astype(np.float32) / np.float32(255.0)) for k, v in g8.items()}
+                image, now, nxt = f(3), f(ev_c), f(ev_c)
+                c = 0.23
+                # the oracle takes RGB event views; a luma view is its own luma: hand it (Y, Y, Y) / (w . 1) ... or RGB directly
+                if ev_c == 1:
+                    w = np.array([0.4124, 0.35758, 0.1804], np.float32)
+                    now3 = np.repeat(now, 3, 0) / np.float32(w.sum())
+                    nxt3 = np.repeat(nxt, 3, 0) / np.float32(w.sum())
+                else:
+                    now3, nxt3 = now, nxt
+                loss, g = lo.event_loss(image, now3, nxt3, gf["event_now"], gf["event_next"], gf["intensity"], c,
+                                        gf["blurry"] if deblur else None)
+                T = lambda a: torch.tensor(a).to(cuda_dev).contiguous()
+                for gt in (gf, g8):
+                    out, seeds = fused.event_loss_and_seeds(T(image), T(now), T(nxt), {k: T(v) for k, v in gt.items()},
+                                                            torch.tensor(c, device=cuda_dev), deblur)
+                    tag = (H, W, deblur, ev_c, gt is g8)
+                    assert abs(out[0].item() - loss) <= 2e-5 * abs(loss), tag
+                    assert rel_err(seeds["image"].cpu().numpy(), g["image"]) < 1e-5, tag
+                    if ev_c == 3:
+                        assert rel_err(seeds["image_now"].cpu().numpy(), g["image_now"], 1e-12) < 1e-4, tag
+                        assert rel_err(seeds["image_next"].cpu().numpy(), g["image_next"], 1e-12) < 1e-4, tag
+                    else:               # a luma view's seed is dL/dY itself: the oracle's red channel over its luma weight
+                        assert rel_err(seeds["image_now"].cpu().numpy()[0], g["image_now"][0] / 0.4124, 1e-12) < 1e-4, tag
+                        assert rel_err(seeds["image_next"].cpu().numpy()[0], g["image_next"][0] / 0.4124, 1e-12) < 1e-4, tag
+
+
 def test_dist2_matches_bruteforce_oracle(cuda_dev):
     """distCUDA2 replacement against the exact brute-force oracle (parity unpinned by the reference:
     simple-knn is not in its tree)."""
